@@ -1,0 +1,129 @@
+/*
+ * ngp_b200.h -- C ABI of the B200-native Instant-NGP inference renderer.
+ *
+ * This is the drop-in boundary for the hot path of sisl/NeRFSafetyValidation
+ * (NeRFRenderer.render(cuda_ray=True), inference branch).  Every entry point replaces one function the
+ * reference exports from its pybind11 extensions (file:line below are relative to the reference root);
+ * the signatures are the reference's, with at::Tensor replaced by a raw DEVICE pointer + sizes and an
+ * explicit stream (the reference launches everything on the legacy default stream).
+ *
+ * Conventions
+ *   - All pointers are device pointers unless the name ends in `_host`.
+ *   - The caller owns every buffer; the library allocates nothing except inside an ngp_ctx
+ *     (explicitly created / destroyed workspace for the fused path).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - Every function returns 0 on success, non-zero on error; ngp_last_error() then describes it
+ *     (thread-local).  Nothing throws across the boundary.  There is NO CPU fallback.
+ *   - Kernels are enqueued asynchronously; only *_host entry points and ngp_ctx_* synchronise.
+ */
+#ifndef NGP_B200_H
+#define NGP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NGP_ABI_VERSION 1
+
+#define NGP_DTYPE_F32 0
+#define NGP_DTYPE_F16 1
+
+int ngp_abi_version(void);
+const char *ngp_last_error(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches claim) */
+uint64_t ngp_launch_count(void);
+
+/* ---------------------------------------------------------------- raymarching (inference + setup)
+ * replaces _raymarching.{near_far_from_aabb, morton3D, morton3D_invert, packbits, march_rays,
+ * composite_rays}: raymarching/src/bindings.cpp:5-18, raymarching/src/raymarching.h:7-18 */
+
+/* raymarching/src/raymarching.cu:93-158.  aabb: device float[6]. Misses write FLT_MAX to both. */
+int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, uint32_t N,
+                           float min_near, float *nears, float *fars, void *stream);
+/* raymarching/src/raymarching.cu:216-235 */
+int ngp_morton3D(const int32_t *coords, uint32_t N, int32_t *indices, void *stream);
+/* raymarching/src/raymarching.cu:240-262 */
+int ngp_morton3D_invert(const int32_t *indices, uint32_t N, int32_t *coords, void *stream);
+/* raymarching/src/raymarching.cu:269-302.  N = number of output BYTES (C*H^3/8). */
+int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream);
+/* raymarching/src/raymarching.cu:706-825.  xyzs/dirs/deltas must be pre-zeroed by the caller
+ * (raymarching.py:329-331).  perturb must be 0 (validate.py:290 never perturbs at inference). */
+int ngp_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t *rays_alive, const float *rays_t,
+                   const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps,
+                   uint32_t C, uint32_t H, const uint8_t *grid, const float *nears, const float *fars,
+                   float *xyzs, float *dirs, float *deltas, uint32_t perturb, void *stream);
+/* raymarching/src/raymarching.cu:828-922.  In place on rays_alive, rays_t, weights_sum, depth, image. */
+int ngp_composite_rays(uint32_t n_alive, uint32_t n_step, int32_t *rays_alive, float *rays_t,
+                       const float *sigmas, const float *rgbs, const float *deltas, float *weights_sum,
+                       float *depth, float *image, void *stream);
+/* nerf/renderer.py:369 `rays_alive = rays_alive[rays_alive >= 0]` as a stable, sync-free stream compaction
+ * (warp ballot + block scan + decoupled look-back).  d_count: device uint32 receiving the survivor count.
+ * d_scratch: device scratch of at least ngp_compact_scratch_bytes(n) bytes (contents irrelevant). */
+uint64_t ngp_compact_scratch_bytes(uint32_t n);
+int ngp_compact_alive(const int32_t *in, uint32_t n, int32_t *out, uint32_t *d_count, void *d_scratch,
+                      void *stream);
+
+/* ---------------------------------------------------------------- encoders
+ * replaces _gridencoder.grid_encode_forward (gridencoder/src/bindings.cpp:5-8, gridencoder.cu:423-446)
+ * for D=3, calc_grad_inputs=False.  table_dtype selects float / half table AND output dtype, like the
+ * reference's AT_DISPATCH.  out_layout 0 = [L,B,C] (the reference kernel's), 1 = [B,L*C] (what
+ * grid.py:52 permutes to; saves the permute copy).  Half tables: ref_rounding=1 reproduces the reference's
+ * round-to-half after every corner (gridencoder.cu:143,166) bit for bit; 0 accumulates in fp32.
+ * idx_out: optional int32 [L,B,8] receiving the table rows gathered (integer parity hook), or NULL. */
+int ngp_grid_encode_forward(const float *inputs01, const void *table, int table_dtype, const int32_t *offsets,
+                            void *outputs, uint32_t B, uint32_t D, uint32_t C, uint32_t L, float S, uint32_t H,
+                            uint32_t gridtype, int align_corners, int out_layout, int ref_rounding,
+                            int32_t *idx_out, void *stream);
+/* per-level `scale = exp2f(level*S)*H - 1` exactly as the device computes it (gridencoder.cu:126) */
+int ngp_grid_level_scales(uint32_t L, float S, uint32_t H, float *scales, void *stream);
+/* replaces _shencoder.sh_encode_forward (shencoder/src/shencoder.cu:388-419), degree 1..4, fp32 */
+int ngp_sh_encode_forward(const float *inputs, float *outputs, uint32_t B, uint32_t degree, void *stream);
+
+/* ---------------------------------------------------------------- fully fused MLP
+ * replaces _ffmlp.ffmlp_inference (ffmlp/src/ffmlp.cu:673-709) for hidden_dim=64, ReLU, output_dim=16:
+ * inputs [B,in_dim] half (B % 128 == 0, in_dim in {32,64}), weights = contiguous row-major
+ * [64][in_dim] + (num_layers-1) x [64][64] + [16][64] halves (ffmlp.py:121), outputs [B,16] half.
+ * fp16 operands, fp32 accumulation on tensor cores. */
+int ngp_ffmlp_inference(const void *inputs_f16, const void *weights_f16, uint32_t B, uint32_t input_dim,
+                        uint32_t output_dim, uint32_t hidden_dim, uint32_t num_layers, uint32_t activation,
+                        uint32_t output_activation, void *outputs_f16, void *stream);
+
+/* ---------------------------------------------------------------- fused path (no upstream counterpart)
+ * One context = one model resident on one device: half hash table, offsets, both MLPs, occupancy
+ * bitfield, plus a ray-state workspace that grows to the largest N seen. */
+typedef struct ngp_ctx ngp_ctx;
+
+int ngp_ctx_create(ngp_ctx **ctx);
+int ngp_ctx_destroy(ngp_ctx *ctx);
+/* Registers the network of nerf/network_ff.py:11-49 (hashgrid L levels x 2 ch -> sigma_net -> SH4 + colour net).
+ * Pointers are borrowed (must stay valid); offsets_host is a HOST int32[L+1]. */
+int ngp_ctx_set_network(ngp_ctx *ctx, const void *table_f16, const int32_t *offsets_dev,
+                        const int32_t *offsets_host, uint32_t L, float S, uint32_t H,
+                        const void *w_sigma_f16, uint32_t nl_sigma, const void *w_color_f16,
+                        uint32_t nl_color, float bound, float density_scale, void *stream);
+/* nerf/renderer.py:73-99 state: bitfield [cascade*grid^3/8] bytes (borrowed), aabb = HOST float[6]. */
+int ngp_ctx_set_scene(ngp_ctx *ctx, const uint8_t *bitfield, uint32_t cascade, uint32_t grid_size,
+                      const float *aabb_host, float min_near);
+/* NeRFNetwork.forward (nerf/network_ff.py:51-74) + `sigmas *= density_scale` (renderer.py:365) in one kernel:
+ * xyzs,dirs [M,3] fp32 -> sigmas [M] fp32, rgbs [M,3] fp32.  Any M >= 0 (rows padded internally). */
+int ngp_network_forward(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint32_t M, float *sigmas,
+                        float *rgbs, void *stream);
+/* NeRFRenderer.run_cuda, inference branch (nerf/renderer.py:261-284,329-386) as ONE persistent launch:
+ * near/far -> loop{march -> encode -> MLPs -> composite -> stable compaction, global n_step schedule} ->
+ * background mix + depth normalisation.  image [N,3], depth [N], weights_sum [N] fp32 (any may not be NULL).
+ * samples_per_ray: optional int32 [N]; stats: optional device int64[4] = {iterations, samples, tiles, 0}. */
+int ngp_render(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma,
+               uint32_t max_steps, float bg_color, float *image, float *depth, float *weights_sum,
+               int32_t *samples_per_ray, int64_t *stats, void *stream);
+/* Same, HOST buffers in and out: H2D of rays, render, D2H of image/depth; synchronous.  This is the call the
+ * end-to-end number in bench.py is measured through. */
+int ngp_render_host(ngp_ctx *ctx, const float *rays_o_host, const float *rays_d_host, uint32_t N,
+                    float dt_gamma, uint32_t max_steps, float bg_color, float *image_host, float *depth_host,
+                    void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NGP_B200_H */

@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""bench.py -- rendered Mrays/s of the NGP `cuda_ray` inference path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg5|rollout]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of the hot path over one batch of synthetic rays:
+    cfg2 (default)  one 800x800 frame of the Stonehenge-shaped scene, 16-level 2^19 hash grid + SH + 64-wide MLPs,
+                    variant-A weights (reference init), max_steps 1024, dt_gamma 0, bg 1   (BASELINE.json configs[1])
+Every rank renders its own camera of the same orbit (disturbance rollouts / camera batches shard with replicated
+weights, no data-path collective) => weak scaling; `value` = rays of all ranks / max-over-ranks time.
+
+`value`    device-resident inputs, CUDA events around ngp_render on the launching stream, L2 flushed between steps.
+`e2e`      the same frame through ngp_render_host: pinned host rays -> H2D -> render -> D2H image+depth, inside the timer.
+`roofline` dominant kernel = k_render (the only kernel of a step): algorithmic 512 B gathered per sample x samples
+           counted by the kernel, over the measured HBM copy peak (MEASURED_PEAKS.json).  The 2^19 table (23.3 MB fp16)
+           is L2-resident on B200, so frac > 1 is possible and is discussed in DESIGN.md.
+`cpu_baseline`  oracle/ngp_oracle.c (OpenMP port of the reference path) on a strided sub-sample of the same frame.
+`--impl reference`  the same CPU port on all host threads, as the reference arm (the reference has no CPU
+           implementation of the NGP path; its CUDA extensions rebuilt for sm_100a are timed beside it as `reference_gpu`).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (H, W, focal, log2T, dense_bitfield)
+    "cfg2": dict(H=800, W=800, focal=1111.11, log2T=19, dense=False,
+                 desc="cfg2: 800x800 Stonehenge-shaped frame, NGP L16 T2^19 F2 + SH4 + 64-wide ffmlp, bound 1, max_steps 1024"),
+    "cfg5": dict(H=1080, W=1920, focal=1500.0, log2T=22, dense=True,
+                 desc="cfg5: 1920x1080 frame, T2^22 table, dense occupancy, max_steps 1024"),
+    "rollout": dict(H=200, W=200, focal=277.78, log2T=19, dense=False, frames=64,
+                    desc="cfg3 batch: 64 rollout frames of 200x200 per render call"),
+}
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--workload", default="cfg2", choices=list(WORKLOADS))
+    p.add_argument("--variant", default="A", choices=["A", "B"])
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-ref-gpu", action="store_true")
+    p.add_argument("--cpu-rays", type=int, default=0, help="rays in the CPU sample (0 = auto)")
+    return p.parse_args()
+
+
+def frame_rays(wl, rank, n_frames=1):
+    """rays of rank `rank`'s frame(s): cameras on the cfg2 orbit, azimuth advanced per rank/frame (a stand-in for the
+    per-rollout poses of validate.py's disturbance rollouts)."""
+    from nerfsafetyvalidation_b200 import synthetic as syn
+    os_, ds_ = [], []
+    for f in range(n_frames):
+        az = 37.0 + 45.0 * rank + (360.0 / max(n_frames, 1)) * f
+        o, d = syn.pinhole_rays(syn.orbit_pose(az), wl["H"], wl["W"], focal=wl["focal"])
+        os_.append(o)
+        ds_.append(d)
+    return np.concatenate(os_), np.concatenate(ds_)
+
+
+def scene_for(wl):
+    from nerfsafetyvalidation_b200 import synthetic as syn
+    bitfield, grid = syn.stonehenge_bitfield()
+    if wl["dense"]:
+        bitfield = np.full_like(bitfield, 255)
+    return bitfield, grid
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], threading.Event()
+        self.thread = threading.Thread(target=self.run, daemon=True)
+
+    def sample(self):
+        try:
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                 capture_output=True, text=True, timeout=5).stdout.strip()
+            if out:
+                self.rows.append([c.strip() for c in out.splitlines()[0].split(",")])
+        except Exception:
+            pass
+
+    def run(self):
+        while not self.stop.is_set():
+            self.sample()
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.thread.join(timeout=10)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[5:9]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_port_mrays(wl, variant, n_rays, threads=None):
+    """oracle/ngp_oracle.c on a strided sub-sample of rank 0's frame.  Returns (Mrays/s, seconds, rays, threads)."""
+    from nerfsafetyvalidation_b200 import synthetic as syn
+    from oracle import oracle as orc
+    if threads:
+        os.environ["OMP_NUM_THREADS"] = str(threads)
+    bitfield, _ = scene_for(wl)
+    w = syn.ngp_weights(0, log2_hashmap_size=wl["log2T"], variant=variant)
+    o, d = frame_rays(wl, 0)
+    stride = max(1, o.shape[0] // n_rays)
+    o, d = np.ascontiguousarray(o[::stride]), np.ascontiguousarray(d[::stride])
+    aabb = np.array([-1, -1, -1, 1, 1, 1], np.float32)
+    t0 = time.perf_counter()
+    r = orc.render(o, d, aabb, bitfield, w["table"], w["offsets"], w["S"], 16, w["w_sigma"], w["w_color"],
+                   density_scale=w["density_scale"])
+    dt = time.perf_counter() - t0
+    return o.shape[0] / dt / 1e6, dt, o.shape[0], r
+
+
+def run_reference_arm(args, wl):
+    """--impl reference: the CPU port of the reference path on all host threads, same metric / unit / config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    n = args.cpu_rays or 20000
+    vals, secs = [], []
+    for i in range(args.warmup + args.steps):
+        v, dt, rays, _ = cpu_port_mrays(wl, args.variant, n)
+        if i >= args.warmup:
+            vals.append(v)
+            secs.append(dt)
+        if sum(secs) > 150:   # keep the whole run within a few minutes
+            break
+    value = rays * len(secs) / sum(secs) / 1e6
+    line = {"metric": "rendered Mrays/s (NGP hashgrid, cuda_ray inference)", "value": value, "unit": "Mrays/s", "impl": "reference",
+            "n_gpus": args.gpus, "steps": len(secs), "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
+            "config": {"workload": wl["desc"], "variant": args.variant},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port",
+                             "sample": f"{rays} rays (every {max(1, wl['H'] * wl['W'] // n)}th ray of the frame) per step, oracle/ngp_oracle.c with OpenMP"},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    args = parse()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        return run_reference_arm(args, wl)
+
+    import torch
+    import torch.distributed as dist
+
+    from nerfsafetyvalidation_b200 import _cabi, synthetic as syn
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this framework has no CPU fallback (use --impl reference for the CPU port)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- model: rank 0 builds the weights, everyone else receives them with ONE broadcast (replicated weights)
+    bitfield, grid = scene_for(wl)
+    w = syn.ngp_weights(0 if rank == 0 else 1, log2_hashmap_size=wl["log2T"], variant=args.variant)
+    model = syn.build_model(w, bitfield, grid, device=dev)
+    if world > 1:
+        for t in (model.encoder.embeddings.data, model.sigma_net.weights.data, model.color_net.weights.data, model.density_bitfield):
+            dist.broadcast(t, src=0)
+        model.encoder._half = model.sigma_net._half = model.color_net._half = None
+    lib = _cabi.load()
+
+    n_frames = wl.get("frames", 1)
+    o_np, d_np = frame_rays(wl, rank, n_frames)
+    N = o_np.shape[0]
+    o_dev, d_dev = torch.from_numpy(o_np).to(dev), torch.from_numpy(d_np).to(dev)
+    o_pin, d_pin = torch.from_numpy(o_np).pin_memory(), torch.from_numpy(d_np).pin_memory()
+    img_pin = torch.empty(N, 3, dtype=torch.float32).pin_memory()
+    dep_pin = torch.empty(N, dtype=torch.float32).pin_memory()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def render_dev(stats=False):
+        with torch.no_grad():
+            return model.render(o_dev.view(1, N, 3), d_dev.view(1, N, 3), bg_color=1, perturb=False, dt_gamma=0, max_steps=1024,
+                                return_stats=stats)
+
+    def render_host():
+        model._configure_native(model._native)
+        h = model._native.get()
+        model._set_scene(model._native, h)
+        _cabi.check(lib.ngp_render_host(h, _cabi.ptr(o_pin), _cabi.ptr(d_pin), N, 0.0, 1024, 1.0, _cabi.ptr(img_pin), _cabi.ptr(dep_pin),
+                                        _cabi.stream()), "ngp_render_host")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, host_timer=False):
+        """K steps, L2 flushed before each, each step timed on the device (events) or on the host (sync call)."""
+        total = 0.0
+        for _ in range(steps):
+            flush.zero_()
+            if host_timer:
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                fn()
+                total += (time.perf_counter() - t0) * 1e3
+            else:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                fn()
+                e1.record()
+                e1.synchronize()
+                total += e0.elapsed_time(e1)
+        return total
+
+    # ---- warm-up (also counts samples / iterations once)
+    out = render_dev(stats=True)
+    torch.cuda.synchronize()
+    stats = out["stats"].cpu().tolist()
+    iters, samples = int(stats[0]), int(stats[1])
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        render_dev()
+        render_host()
+
+    # ---- timed: device-resident
+    barrier()
+    launches0 = _cabi.launch_count()
+    with ClockSampler(local) as clocks:
+        ms_dev = timed(render_dev, args.steps)
+        barrier()
+        launches = _cabi.launch_count() - launches0
+        ms_e2e = timed(render_host, args.steps, host_timer=True)
+        barrier()
+    if world > 1:
+        t = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e = t.tolist()
+        cnt = torch.tensor([N, samples], dtype=torch.int64, device=dev)
+        dist.all_reduce(cnt)
+        rays_all, samples_all = cnt.tolist()
+    else:
+        rays_all, samples_all = N, samples
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        ms_step = ms_dev / args.steps
+        value = rays_all / (ms_step * 1e-3) / 1e6
+        e2e_value = rays_all / (ms_e2e / args.steps * 1e-3) / 1e6
+        achieved = samples * 512 / (ms_step * 1e-3) / 1e9    # this rank's kernel: its own samples / its own launch time
+        line = {"metric": "rendered Mrays/s (NGP hashgrid, cuda_ray inference)", "value": value, "unit": "Mrays/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
+                "config": {"workload": wl["desc"], "variant": args.variant, "rays_per_gpu_per_step": N, "samples_per_step": samples,
+                           "samples_per_ray": samples / N, "iterations_per_step": iters, "frames_per_step": n_frames,
+                           "l2": "flushed between steps (256 MB write)", "parallelism": f"replicated weights, {world} ray shards"},
+                "frames_per_s": n_frames * world / (ms_step * 1e-3), "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(o_pin.numel() * 4 + d_pin.numel() * 4),
+                        "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_e2e / args.steps,
+                        "api": "ngp_render_host (C ABI, pinned host buffers)"},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                             "traffic": None, "kernel": "k_render", "algorithmic_bytes_per_sample": 512,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                             "tensor_tflops_achieved": samples * 36864 / (ms_step * 1e-3) / 1e12},
+                "clocks": clocks.summary()}
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            n = args.cpu_rays or 20000
+            v, dt, rays, _ = cpu_port_mrays(wl, args.variant, n)
+            line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port", "seconds": dt,
+                                    "sample": f"{rays} rays (strided sub-sample of the same frame), oracle/ngp_oracle.c, OpenMP"}
+        if world == 1 and not args.no_ref_gpu:
+            line["reference_gpu"] = reference_gpu(wl, w, bitfield, o_dev, d_dev, flush, dev)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def reference_gpu(wl, w, bitfield, o_dev, d_dev, flush, dev):
+    """The reference's own extensions rebuilt for sm_100a (oracle/_ref), driven by its run_cuda loop, same frame, same box."""
+    import torch
+    try:
+        from tests import refext
+        if not refext.available("_ffmlp"):
+            return {"unavailable": "oracle/_ref/*.so not built"}
+        ref = refext.RefModel(w, bitfield, device=dev)
+        ref.run_cuda(o_dev, d_dev)
+        times = []
+        for _ in range(3):
+            flush.zero_()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = ref.run_cuda(o_dev, d_dev)
+            torch.cuda.synchronize()
+            times.append(time.perf_counter() - t0)
+        t = min(times)
+        return {"value": o_dev.shape[0] / t / 1e6, "unit": "Mrays/s", "ms_per_step": t * 1e3, "iterations": r["iterations"],
+                "samples": r["samples"], "what": "reference _raymarching/_gridencoder/_shencoder/_ffmlp rebuilt for sm_100a + run_cuda loop"}
+    except Exception as e:  # the oracle is optional evidence, never the product
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

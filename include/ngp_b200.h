@@ -24,6 +24,10 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+/* the library is built with -fvisibility=hidden; exactly the entry points declared here are exported */
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define NGP_ABI_VERSION 1
 
@@ -106,10 +110,11 @@ int ngp_ctx_set_network(ngp_ctx *ctx, const void *table_f16, const int32_t *offs
 /* nerf/renderer.py:73-99 state: bitfield [cascade*grid^3/8] bytes (borrowed), aabb = HOST float[6]. */
 int ngp_ctx_set_scene(ngp_ctx *ctx, const uint8_t *bitfield, uint32_t cascade, uint32_t grid_size,
                       const float *aabb_host, float min_near);
-/* NeRFNetwork.forward (nerf/network_ff.py:51-74) + `sigmas *= density_scale` (renderer.py:365) in one kernel:
- * xyzs,dirs [M,3] fp32 -> sigmas [M] fp32, rgbs [M,3] fp32.  Any M >= 0 (rows padded internally). */
-int ngp_network_forward(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint32_t M, float *sigmas,
-                        float *rgbs, void *stream);
+/* NeRFNetwork.forward (nerf/network_ff.py:51-74) in one kernel: xyzs,dirs [M,3] fp32 -> sigmas [M] fp32,
+ * rgbs [M,3] fp32.  apply_density_scale != 0 also folds in `sigmas *= density_scale` (renderer.py:365).
+ * Any M >= 0 (rows padded internally). */
+int ngp_network_forward(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint32_t M, int apply_density_scale,
+                        float *sigmas, float *rgbs, void *stream);
 /* NeRFRenderer.run_cuda, inference branch (nerf/renderer.py:261-284,329-386) as ONE persistent launch:
  * near/far -> loop{march -> encode -> MLPs -> composite -> stable compaction, global n_step schedule} ->
  * background mix + depth normalisation.  image [N,3], depth [N], weights_sum [N] fp32 (any may not be NULL).
@@ -123,6 +128,9 @@ int ngp_render_host(ngp_ctx *ctx, const float *rays_o_host, const float *rays_d_
                     float dt_gamma, uint32_t max_steps, float bg_color, float *image_host, float *depth_host,
                     void *stream);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -32,7 +32,7 @@ _SIGNATURES = {
     "ngp_ctx_destroy": [_p],
     "ngp_ctx_set_network": [_p, _p, _p, _p, _u32, _f32, _u32, _p, _u32, _p, _u32, _f32, _f32, _p],
     "ngp_ctx_set_scene": [_p, _p, _u32, _u32, _p, _f32],
-    "ngp_network_forward": [_p, _p, _p, _u32, _p, _p, _p],
+    "ngp_network_forward": [_p, _p, _p, _u32, _i32, _p, _p, _p],
     "ngp_render": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render_host": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p],
 }

@@ -553,13 +553,16 @@ int ngp_ctx_set_scene(ngp_ctx *c, const uint8_t *bitfield, uint32_t cascade, uin
     return 0;
 }
 
-int ngp_network_forward(ngp_ctx *c, const float *xyzs, const float *dirs, uint32_t M, float *sigmas, float *rgbs, void *stream) {
+int ngp_network_forward(ngp_ctx *c, const float *xyzs, const float *dirs, uint32_t M, int apply_density_scale, float *sigmas,
+                        float *rgbs, void *stream) {
     NGP_REQUIRE(c != nullptr && c->has_net, "network_forward: ngp_ctx_set_network has not been called");
     if (M == 0) return 0;
     NGP_DEVPTR(xyzs); NGP_DEVPTR(dirs); NGP_DEVPTR(sigmas); NGP_DEVPTR(rgbs);
     const uint32_t n_tiles = div_up(M, kTile);
     const uint32_t grid = n_tiles < (uint32_t)c->fwd_blocks ? n_tiles : (uint32_t)c->fwd_blocks;
-    k_network_forward<<<grid, kTile, c->fwd_smem, as_stream(stream)>>>(c->nc, xyzs, dirs, M, sigmas, rgbs, n_tiles);
+    NetConst nc = c->nc;
+    if (!apply_density_scale) nc.density_scale = 1.0f;
+    k_network_forward<<<grid, kTile, c->fwd_smem, as_stream(stream)>>>(nc, xyzs, dirs, M, sigmas, rgbs, n_tiles);
     return after_launch("network_forward");
 }
 

@@ -1,0 +1,130 @@
+"""Drop-in for the reference's nerf/network_ff.py: `NeRFNetwork` (hash grid -> sigma FFMLP -> SH -> colour FFMLP).
+
+Same constructor, sub-module names (`encoder`, `sigma_net`, `encoder_dir`, `color_net`, so checkpoints load with the
+reference's state-dict keys) and the same `forward / density / color` surface.  `forward` is one fused kernel
+(ngp_network_forward); `density` and `color` compose the stand-alone encoders and MLP.
+
+dtype flow = the reference's under fp16 autocast (grid.py:38-39, ffmlp.py:18, activation.py:5-10): half table, half
+activations, sigma = exp in fp32, rgb = sigmoid rounded to half.  We run that flow with or without autocast
+(validate.py:290 does not enter autocast, where the reference's --ff model would fail CHECK_IS_HALF).
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from .. import _cabi
+from ..activation import trunc_exp
+from ..encoding import get_encoder
+from ..ffmlp import FFMLP
+from .renderer import NeRFRenderer
+
+
+class NeRFNetwork(NeRFRenderer):
+    def __init__(self, encoding="hashgrid", encoding_dir="sphere_harmonics", num_layers=2, hidden_dim=64, geo_feat_dim=15,
+                 num_layers_color=3, hidden_dim_color=64, bound=1, log2_hashmap_size=19, **kwargs):
+        super().__init__(bound, **kwargs)
+        self.num_layers = num_layers
+        self.hidden_dim = hidden_dim
+        self.geo_feat_dim = geo_feat_dim
+        self.encoder, self.in_dim = get_encoder(encoding, desired_resolution=2048 * bound, log2_hashmap_size=log2_hashmap_size)
+        self.sigma_net = FFMLP(input_dim=self.in_dim, output_dim=1 + self.geo_feat_dim, hidden_dim=self.hidden_dim,
+                               num_layers=self.num_layers)
+        self.num_layers_color = num_layers_color
+        self.hidden_dim_color = hidden_dim_color
+        self.encoder_dir, self.in_dim_color = get_encoder(encoding_dir)
+        self.in_dim_color += self.geo_feat_dim + 1  # padded to 32, network_ff.py:41
+        self.color_net = FFMLP(input_dim=self.in_dim_color, output_dim=3, hidden_dim=self.hidden_dim_color,
+                               num_layers=self.num_layers_color)
+
+    # ------------------------------------------------------------------ fused path
+    def _fusable(self):
+        from ..gridencoder import GridEncoder
+        from ..shencoder import SHEncoder
+        e = self.encoder
+        return (isinstance(e, GridEncoder) and isinstance(self.encoder_dir, SHEncoder) and e.num_levels == 16 and e.level_dim == 2
+                and e.gridtype_id == 0 and not e.align_corners and self.encoder_dir.degree == 4 and self.hidden_dim == 64
+                and self.hidden_dim_color == 64 and self.geo_feat_dim == 15 and 2 <= self.num_layers <= 4
+                and 2 <= self.num_layers_color <= 4)
+
+    def _configure_native(self, owner):
+        if not self._fusable() or not self.encoder.embeddings.is_cuda:
+            return False
+        lib = _cabi.load()
+        table = self.encoder.half_table()
+        ws, wc = self.sigma_net.half_weights(), self.color_net.half_weights()
+        key = (table.data_ptr(), ws.data_ptr(), wc.data_ptr(), self.encoder.embeddings._version, self.sigma_net.weights._version,
+               self.color_net.weights._version, float(self.bound), float(self.density_scale))
+        if owner.keys is not None and owner.keys.get("net") == key:
+            return True
+        handle = owner.get()
+        offs_host = self.encoder.offsets.detach().cpu().numpy().astype(np.int32)
+        offs_dev = self.encoder.offsets.int().contiguous()
+        S = float(np.log2(self.encoder.per_level_scale))
+        _cabi.check(lib.ngp_ctx_set_network(handle, _cabi.ptr(table), _cabi.ptr(offs_dev), offs_host.ctypes.data_as(C.c_void_p),
+                                            self.encoder.num_levels, S, int(self.encoder.base_resolution), _cabi.ptr(ws),
+                                            self.num_layers, _cabi.ptr(wc), self.num_layers_color, float(self.bound),
+                                            float(self.density_scale), _cabi.stream()), "ngp_ctx_set_network")
+        owner.keys = dict(owner.keys or {}, net=key)
+        owner.keep = (table, ws, wc, offs_dev)
+        return True
+
+    def forward(self, x, d):
+        """network_ff.py:51-74: x [N,3] in [-bound,bound], d [N,3] -> (sigma [N] fp32, rgb [N,3]).
+        sigma is NOT multiplied by density_scale here (renderer.py:365 does that); ngp_render folds it in itself."""
+        if self._configure_native(self._native):
+            lib = _cabi.load()
+            _cabi.require_cuda(x, d)
+            x = x.float().contiguous().view(-1, 3)
+            d = d.float().contiguous().view(-1, 3)
+            M = x.shape[0]
+            sig = torch.empty(M, dtype=torch.float32, device=x.device)
+            rgb = torch.empty(M, 3, dtype=torch.float32, device=x.device)
+            _cabi.check(lib.ngp_network_forward(self._native.get(), _cabi.ptr(x), _cabi.ptr(d), M, 0, _cabi.ptr(sig), _cabi.ptr(rgb),
+                                                _cabi.stream()), "ngp_network_forward")
+            return sig, rgb
+        return self._forward_unfused(x, d)
+
+    def _forward_unfused(self, x, d):
+        x = self.encoder(x, bound=self.bound)
+        h = self.sigma_net(x)
+        sigma = trunc_exp(h[..., 0])
+        geo_feat = h[..., 1:]
+        d = self.encoder_dir(d)
+        p = torch.zeros_like(geo_feat[..., :1])
+        h = torch.cat([d.to(geo_feat.dtype), geo_feat, p], dim=-1)
+        h = self.color_net(h)
+        rgb = torch.sigmoid(h.float()).to(h.dtype)
+        return sigma, rgb
+
+    def density(self, x):
+        """network_ff.py:76-89"""
+        x = self.encoder(x, bound=self.bound)
+        h = self.sigma_net(x)
+        sigma = trunc_exp(h[..., 0])
+        geo_feat = h[..., 1:]
+        return {"sigma": sigma, "geo_feat": geo_feat}
+
+    def color(self, x, d, mask=None, geo_feat=None, **kwargs):
+        """network_ff.py:92-134 (masked inference allowed)"""
+        if mask is not None:
+            rgbs = torch.zeros(mask.shape[0], 3, dtype=x.dtype, device=x.device)
+            if not mask.any():
+                return rgbs
+            x = x[mask]
+            d = d[mask]
+            geo_feat = geo_feat[mask]
+        d = self.encoder_dir(d)
+        p = torch.zeros_like(geo_feat[..., :1])
+        h = torch.cat([d.to(geo_feat.dtype), geo_feat, p], dim=-1)
+        h = self.color_net(h)
+        h = torch.sigmoid(h.float()).to(h.dtype)
+        if mask is not None:
+            rgbs[mask] = h.to(rgbs.dtype)
+        else:
+            rgbs = h
+        return rgbs
+
+    def get_params(self, lr):
+        return [{"params": self.encoder.parameters(), "lr": lr}, {"params": self.sigma_net.parameters(), "lr": lr},
+                {"params": self.encoder_dir.parameters(), "lr": lr}, {"params": self.color_net.parameters(), "lr": lr}]

@@ -1,0 +1,239 @@
+"""Drop-in for the inference side of the reference's nerf/renderer.py: `NeRFRenderer`.
+
+`render(rays_o, rays_d, staged=False, max_ray_batch=4096, **kwargs)` and `run_cuda(...)` keep the reference's
+signatures and result dict (nerf/renderer.py:261-386, 549-588).  Two execution modes for the inference branch:
+
+  fused (default)   the whole loop of renderer.py:329-376 is ONE persistent cooperative kernel (ngp_render):
+                    near/far -> {march -> hash-grid -> MLPs -> composite -> stable compaction} with the reference's
+                    global `n_step = clamp(N // n_alive, 1, 8)` schedule evaluated on the device, then background
+                    mix and depth normalisation.  No host sync, no intermediate tensors in HBM.
+  stepwise          the reference's Python loop verbatim, on our stand-alone ops (one launch per op per
+                    iteration); kept for kernel-boundary parity tests (`fused=False`).
+
+Only the `cuda_ray=True` eval path is built; training and the PyTorch sampler `run()` raise.
+"""
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from .. import _cabi
+from .. import raymarching
+
+
+class _NativeCtx:
+    """Owner of one ngp_ctx.  Not copied by deepcopy (NerfSimulator.py:37 deep-copies the model): the copy
+    lazily creates its own context on first use."""
+
+    def __init__(self):
+        self.handle = None
+        self.keys = None      # what the context was last configured with
+        self.keep = None      # tensors the context borrows
+
+    def get(self):
+        if self.handle is None:
+            lib = _cabi.load()
+            h = C.c_void_p()
+            _cabi.check(lib.ngp_ctx_create(C.byref(h)), "ngp_ctx_create")
+            self.handle = h
+        return self.handle
+
+    def __deepcopy__(self, memo):
+        return _NativeCtx()
+
+    def __getstate__(self):
+        return {}
+
+    def __setstate__(self, state):
+        self.handle, self.keys, self.keep = None, None, None
+
+    def __del__(self):
+        try:
+            if self.handle is not None:
+                _cabi.load().ngp_ctx_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+class NeRFRenderer(nn.Module):
+    def __init__(self, bound=1, cuda_ray=False, density_scale=1, min_near=0.2, density_thresh=0.01, bg_radius=-1):
+        super().__init__()
+        self.bound = bound
+        self.cascade = 1 + math.ceil(math.log2(bound))
+        self.grid_size = 128
+        self.density_scale = density_scale
+        self.min_near = min_near
+        self.density_thresh = density_thresh
+        self.bg_radius = bg_radius
+
+        aabb_train = torch.tensor([-bound, -bound, -bound, bound, bound, bound], dtype=torch.float32)
+        self.register_buffer("aabb_train", aabb_train)
+        self.register_buffer("aabb_infer", aabb_train.clone())
+
+        self.cuda_ray = cuda_ray
+        if cuda_ray:
+            self.register_buffer("density_grid", torch.zeros([self.cascade, self.grid_size ** 3]))
+            self.register_buffer("density_bitfield", torch.zeros(self.cascade * self.grid_size ** 3 // 8, dtype=torch.uint8))
+            self.mean_density = 0
+            self.iter_density = 0
+            self.register_buffer("step_counter", torch.zeros(16, 2, dtype=torch.int32))
+            self.mean_count = 0
+            self.local_step = 0
+        self._native = _NativeCtx()
+        self.fused = True   # run_cuda default mode
+
+    def forward(self, x, d):
+        raise NotImplementedError()
+
+    def density(self, x):
+        raise NotImplementedError()
+
+    def color(self, x, d, mask=None, **kwargs):
+        raise NotImplementedError()
+
+    def reset_extra_state(self):
+        if not self.cuda_ray:
+            return
+        self.density_grid.zero_()
+        self.mean_density = 0
+        self.iter_density = 0
+        self.step_counter.zero_()
+        self.mean_count = 0
+        self.local_step = 0
+
+    def run(self, rays_o, rays_d, num_steps=128, upsample_steps=128, bg_color=None, perturb=False, **kwargs):
+        raise NotImplementedError("NeRFRenderer.run (cuda_ray=False PyTorch sampler, renderer.py:125-258) is the reference's "
+                                  "CPU-baseline path, not part of the B200 hot path; construct the model with cuda_ray=True")
+
+    # ------------------------------------------------------------------ fused-path plumbing (subclass provides the network)
+    def _configure_native(self, ctx):
+        """Subclasses register their network with the context; returns False if the fused path cannot serve this model."""
+        return False
+
+    def _set_scene(self, ctx_owner, handle):
+        lib = _cabi.load()
+        aabb = self.aabb_train if self.training else self.aabb_infer
+        bf = self.density_bitfield
+        key = (bf.data_ptr(), self.cascade, self.grid_size, tuple(aabb.tolist()), float(self.min_near))
+        if ctx_owner.keys is None or ctx_owner.keys.get("scene") != key:
+            arr = (C.c_float * 6)(*aabb.tolist())
+            _cabi.check(lib.ngp_ctx_set_scene(handle, _cabi.ptr(bf), self.cascade, self.grid_size, arr, float(self.min_near)),
+                        "ngp_ctx_set_scene")
+            ctx_owner.keys = dict(ctx_owner.keys or {}, scene=key)
+
+    def run_cuda(self, rays_o, rays_d, dt_gamma=0, bg_color=None, perturb=False, force_all_rays=False, max_steps=1024,
+                 fused=None, return_stats=False, **kwargs):
+        """nerf/renderer.py:261-386, inference branch.  rays_o, rays_d: [B, N, 3] -> dict(image [B,N,3], depth [B,N], ...)."""
+        if self.training:
+            raise NotImplementedError("run_cuda: the training branch (march_rays_train / composite_rays_train) is outside the "
+                                      "inference hot path built here; call model.eval()")
+        if self.bg_radius > 0:
+            raise NotImplementedError("run_cuda: bg_radius > 0 (background network) is not on the validate.py path (bg_radius=-1)")
+        _cabi.require_cuda(rays_o, rays_d)
+        prefix = rays_o.shape[:-1]
+        rays_o = rays_o.contiguous().view(-1, 3).float()
+        rays_d = rays_d.contiguous().view(-1, 3).float()
+        N = rays_o.shape[0]
+        device = rays_o.device
+        if bg_color is None:
+            bg_color = 1
+        fused = self.fused if fused is None else fused
+        scalar_bg = not torch.is_tensor(bg_color)
+        if fused and not perturb and scalar_bg and self._configure_native(self._native):
+            return self._run_fused(rays_o, rays_d, prefix, N, device, float(dt_gamma), int(max_steps), float(bg_color), return_stats)
+        return self._run_stepwise(rays_o, rays_d, prefix, N, device, dt_gamma, bg_color, perturb, max_steps)
+
+    def _run_fused(self, rays_o, rays_d, prefix, N, device, dt_gamma, max_steps, bg_color, return_stats):
+        lib = _cabi.load()
+        handle = self._native.get()
+        self._set_scene(self._native, handle)
+        image = torch.empty(N, 3, dtype=torch.float32, device=device)
+        depth = torch.empty(N, dtype=torch.float32, device=device)
+        weights_sum = torch.empty(N, dtype=torch.float32, device=device)
+        spr = torch.empty(N, dtype=torch.int32, device=device) if return_stats else None
+        stats = torch.zeros(4, dtype=torch.int64, device=device) if return_stats else None
+        _cabi.check(lib.ngp_render(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
+                                   _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(spr), _cabi.ptr(stats),
+                                   _cabi.stream()), "ngp_render")
+        results = {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum,
+                   # the reference returns the LAST iteration's per-sample tensors (renderer.py:381-382); the fused loop
+                   # never materialises them
+                   "sigmas": None, "rgbs": None}
+        if return_stats:
+            results["samples_per_ray"] = spr
+            results["stats"] = stats
+        return results
+
+    def _run_stepwise(self, rays_o, rays_d, prefix, N, device, dt_gamma, bg_color, perturb, max_steps):
+        with torch.no_grad():
+            nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, self.aabb_train if self.training else self.aabb_infer,
+                                                         self.min_near)
+            weights_sum = torch.zeros(N, dtype=torch.float32, device=device)
+            depth = torch.zeros(N, dtype=torch.float32, device=device)
+            image = torch.zeros(N, 3, dtype=torch.float32, device=device)
+            n_alive = N
+            rays_alive = torch.arange(n_alive, dtype=torch.int32, device=device)
+            rays_t = nears.clone()
+            step = 0
+            sigmas = rgbs = None
+            while step < max_steps:
+                n_alive = rays_alive.shape[0]
+                if n_alive <= 0:
+                    break
+                n_step = max(min(N // n_alive, 8), 1)
+                xyzs, dirs, deltas = raymarching.march_rays(n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, self.bound,
+                                                            self.density_bitfield, self.cascade, self.grid_size, nears, fars, 128,
+                                                            perturb, dt_gamma, max_steps)
+                sigmas, rgbs = self(xyzs, dirs)
+                sigmas = self.density_scale * sigmas
+                raymarching.composite_rays(n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image)
+                rays_alive = raymarching.compact_alive(rays_alive)
+                step += n_step
+            image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
+            depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+        return {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "sigmas": sigmas, "rgbs": rgbs,
+                "weights_sum": weights_sum}
+
+    def render(self, rays_o, rays_d, staged=False, max_ray_batch=4096, **kwargs):
+        """nerf/renderer.py:549-588.  cuda_ray never stages; everything goes to run_cuda in one call."""
+        if not self.cuda_ray:
+            return self.run(rays_o, rays_d, **kwargs)
+        return self.run_cuda(rays_o, rays_d, **kwargs)
+
+    @torch.no_grad()
+    def mark_untrained_grid(self, poses, intrinsic, S=64):
+        raise NotImplementedError("mark_untrained_grid belongs to training-time occupancy maintenance (SURVEY.md section 8f row 4)")
+
+    @torch.no_grad()
+    def update_extra_state(self, decay=0.95, S=128):
+        """nerf/renderer.py:451-546, full-update branch: density query on the 128^3 x cascade grid (jittered cell centres),
+        EMA-max with the running grid, then `packbits` with thresh = min(mean_density, density_thresh)."""
+        if not self.cuda_ray:
+            return
+        dev = self.density_bitfield.device
+        tmp_grid = -torch.ones_like(self.density_grid)
+        ar = torch.arange(self.grid_size, dtype=torch.int32, device=dev)
+        for xs in ar.split(S):
+            for ys in ar.split(S):
+                for zs in ar.split(S):
+                    xx, yy, zz = torch.meshgrid(xs, ys, zs, indexing="ij")
+                    coords = torch.cat([xx.reshape(-1, 1), yy.reshape(-1, 1), zz.reshape(-1, 1)], dim=-1)
+                    indices = raymarching.morton3D(coords).long()
+                    xyzs = 2 * coords.float() / (self.grid_size - 1) - 1
+                    for cas in range(self.cascade):
+                        bound = min(2 ** cas, self.bound)
+                        half_grid_size = bound / self.grid_size
+                        cas_xyzs = xyzs * (bound - half_grid_size)
+                        cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * half_grid_size
+                        sigmas = self.density(cas_xyzs)["sigma"].reshape(-1).detach().float()
+                        sigmas *= self.density_scale
+                        tmp_grid[cas, indices] = sigmas
+        valid_mask = (self.density_grid >= 0) & (tmp_grid >= 0)
+        self.density_grid[valid_mask] = torch.maximum(self.density_grid[valid_mask] * decay, tmp_grid[valid_mask])
+        self.mean_density = torch.mean(self.density_grid.clamp(min=0)).item()
+        self.iter_density += 1
+        density_thresh = min(self.mean_density, self.density_thresh)
+        self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
+        self.local_step = 0

@@ -16,6 +16,7 @@ from nerfsafetyvalidation_b200 import raymarching as our_rm
 from nerfsafetyvalidation_b200 import shencoder as our_sh
 from oracle import oracle as orc
 from tests import refext
+from tests.inputs import grid_inputs, make_rays
 
 pytestmark = pytest.mark.gpu
 
@@ -32,23 +33,6 @@ def assert_bitwise(a, b, what):
     neq = bits(a) != bits(b)
     n = int(neq.sum().item())
     assert n == 0, f"{what}: {n} of {neq.numel()} words differ; first at {neq.flatten().nonzero()[:4].flatten().tolist()}"
-
-
-def make_rays(n, seed, device):
-    """inside/outside origins, axis-parallel directions (d = +-0 -> rcp = +-inf), grazing and missing rays."""
-    g = torch.Generator().manual_seed(seed)
-    o = (torch.rand(n, 3, generator=g) * 4 - 2)
-    o[: n // 4] = torch.rand(n // 4, 3, generator=g) * 1.8 - 0.9           # inside the box
-    d = torch.randn(n, 3, generator=g)
-    d = d / d.norm(dim=-1, keepdim=True)
-    k = n // 16
-    d[:k, 0] = 0.0
-    d[k:2 * k, 1] = -0.0
-    d[2 * k:3 * k] = torch.tensor([0.0, 0.0, 1.0])
-    d[3 * k:4 * k] = torch.tensor([-0.0, 1.0, -0.0])
-    o[4 * k:5 * k, 0] = 1.0                                                # origin on a face
-    d[5 * k:6 * k] = -o[5 * k:6 * k] / o[5 * k:6 * k].norm(dim=-1, keepdim=True)   # aimed at the centre
-    return o.to(device), d.contiguous().to(device)
 
 
 @pytest.fixture(scope="module")
@@ -129,8 +113,8 @@ def test_near_far_bitwise(cuda):
             rn, rf = refext.near_far_from_aabb(o, d, aabb, min_near)
             assert_bitwise(n, rn, "nears vs reference ext")
             assert_bitwise(f, rf, "fars vs reference ext")
-        miss = (n == torch.finfo(torch.float32).max)
-        assert 0 < int(miss.sum()) < n.numel() and torch.equal(miss, f == torch.finfo(torch.float32).max)
+        miss = bits(n) == 0x7F7FFFFF                      # FLT_MAX bit pattern
+        assert 0 < int(miss.sum()) < n.numel() and torch.equal(miss, bits(f) == 0x7F7FFFFF)
 
 
 def test_compact_alive(cuda):
@@ -208,19 +192,6 @@ def test_march_bitwise_random_rays(cuda, scene, bound, dt_gamma, n_step):
 
 
 # ---------------------------------------------------------------------------------------------- encoders / MLP
-def grid_inputs(n, seed, device):
-    g = torch.Generator().manual_seed(seed)
-    x = torch.rand(n, 3, generator=g)
-    x[:64] = 0.0
-    x[64:128] = 1.0
-    x[128:192, 0] = 1.5          # out of bounds -> zeros
-    x[192:256, 2] = -0.25
-    res = torch.tensor([16, 23, 31, 43, 59, 81, 112, 154, 213, 295, 407, 562, 777, 1073, 1483, 2048], dtype=torch.float32)
-    k = torch.randint(0, 16, (1024,), generator=g)
-    x[256:1280, 0] = torch.floor(torch.rand(1024, generator=g) * res[k]) / res[k]   # on cell boundaries
-    return x.to(device)
-
-
 @pytest.mark.parametrize("log2T", [19, 14])
 def test_grid_indices_exact_and_features(cuda, log2T):
     w = syn.ngp_weights(0, log2_hashmap_size=log2T, variant="B")
@@ -370,7 +341,7 @@ def test_render_vs_reference_loop(frame, cuda, variant):
     out = render_ours(ours, o, d)
     img, dep = out["image"][0], out["depth"][0]
     assert img.shape == (o.shape[0], 3) and dep.shape == (o.shape[0],)
-    miss = r["nears"] == torch.finfo(torch.float32).max
+    miss = bits(r["nears"]) == 0x7F7FFFFF
     assert torch.equal(torch.isnan(dep), torch.isnan(r["depth"])), "NaN depth pattern (missed rays: 0/0, renderer.py:376)"
     assert torch.equal(torch.isnan(dep), miss)
     assert (img - r["image"]).abs().max().item() <= 1e-3

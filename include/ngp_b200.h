@@ -110,6 +110,12 @@ int ngp_ctx_set_network(ngp_ctx *ctx, const void *table_f16, const int32_t *offs
 /* nerf/renderer.py:73-99 state: bitfield [cascade*grid^3/8] bytes (borrowed), aabb = HOST float[6]. */
 int ngp_ctx_set_scene(ngp_ctx *ctx, const uint8_t *bitfield, uint32_t cascade, uint32_t grid_size,
                       const float *aabb_host, float min_near);
+/* Diagnostics for the persistent renderer (no upstream counterpart): when enabled, every warp of ngp_render accumulates
+ * clock64() cycles per phase.  ngp_ctx_phase_cycles synchronises the device and copies the 8 sums to HOST memory:
+ * {0 refill/bookkeeping/prologue/epilogue, 1 march, 2 row packing, 3 hash-grid gather, 4 MLPs, 5 composite, 6 grid barrier,
+ *  7 total}, each summed over all warps of all launches since the last reset. */
+int ngp_ctx_enable_profile(ngp_ctx *ctx, int enable);
+int ngp_ctx_phase_cycles(ngp_ctx *ctx, int64_t *out_host, int reset);
 /* NeRFNetwork.forward (nerf/network_ff.py:51-74) in one kernel: xyzs,dirs [M,3] fp32 -> sigmas [M] fp32,
  * rgbs [M,3] fp32.  apply_density_scale != 0 also folds in `sigmas *= density_scale` (renderer.py:365).
  * Any M >= 0 (rows padded internally). */

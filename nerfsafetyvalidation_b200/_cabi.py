@@ -32,6 +32,8 @@ _SIGNATURES = {
     "ngp_ctx_destroy": [_p],
     "ngp_ctx_set_network": [_p, _p, _p, _p, _u32, _f32, _u32, _p, _u32, _p, _u32, _f32, _f32, _p],
     "ngp_ctx_set_scene": [_p, _p, _u32, _u32, _p, _f32],
+    "ngp_ctx_enable_profile": [_p, _i32],
+    "ngp_ctx_phase_cycles": [_p, _p, _i32],
     "ngp_network_forward": [_p, _p, _p, _u32, _i32, _p, _p, _p],
     "ngp_render": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render_host": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p],

@@ -61,9 +61,17 @@ __device__ __forceinline__ bool slab_near_far(float ox, float oy, float oz, floa
 struct MarchConst {
     float bound, dt_gamma, dt_min, dt_max;
     float Hf, Hm1f, rH, H3f, cm1f;  // (float)H, (float)(H-1), 1/(float)H, (float)(H*H*H), (float)(C-1)
+    float mip_b[8], mip_rb[8];      // fminf(1 << level, bound) and its correctly rounded reciprocal (:768-769)
     const uint8_t *grid;
 };
 
+__host__ __device__ __forceinline__ float __frcp_rn_host_or_device(float v) {
+#ifdef __CUDA_ARCH__
+    return __frcp_rn(v);
+#else
+    return 1.0f / v;   // IEEE division on the host == rcp.rn
+#endif
+}
 __host__ __device__ __forceinline__ MarchConst make_march_const(float bound, float dt_gamma, uint32_t max_steps,
                                                                 uint32_t C, uint32_t H, const uint8_t *grid) {
     MarchConst m;
@@ -76,15 +84,21 @@ __host__ __device__ __forceinline__ MarchConst make_march_const(float bound, flo
     m.rH = 1.0f / (float)H;
     m.H3f = (float)(H * H * H);
     m.cm1f = (float)C - 1.0f;
+    for (int l = 0; l < 8; l++) {
+        m.mip_b[l] = fminf((float)(1 << l), bound);
+        m.mip_rb[l] = __frcp_rn_host_or_device(m.mip_b[l]);
+    }
     m.grid = grid;
     return m;
 }
 
-// frexpf exponent clamped to [0, C-1]   (mip_from_pos / mip_from_dt, raymarching.cu:44-56)
+// frexpf exponent clamped to [0, C-1]   (mip_from_pos / mip_from_dt, raymarching.cu:44-56).
+// frexpf's exponent of a normal float is (biased exponent - 126); zero and denormals give <= -126 (clamped to 0 anyway)
+// and CUDA's frexpf returns exponent 0 for inf / nan, so the whole call reduces to integer work on the bit pattern.
 __device__ __forceinline__ int mip_level(float mx, float cm1f) {
-    int e;
-    frexpf(mx, &e);
-    return (int)fminf(cm1f, fmaxf(0.0f, (float)e));
+    const int field = (int)((__float_as_uint(mx) >> 23) & 0xffu);
+    const int e = field == 255 ? 0 : field - 126;
+    return min((int)cm1f, max(0, e));
 }
 
 __device__ __forceinline__ float march_dt(float t, const MarchConst &m) {
@@ -110,44 +124,73 @@ __device__ __forceinline__ float cell_exit(int n, float sgn, float mip_bound, fl
     return __fmul_rn(a, rd);
 }
 
-// Marches one ray from t for up to n_step occupied samples.  emit(step, x, y, z, dt, delta_t) is called per
-// sample.  Returns the number of samples emitted; t_out is the marcher's own t afterwards (NOT what the
-// reference stores in rays_t -- that is advanced by the compositor).
+struct RayDir {   // per-ray constants of the marcher (raymarching.cu:727-731,804-806)
+    float dx, dy, dz, rdx, rdy, rdz, sx, sy, sz;
+};
+__device__ __forceinline__ RayDir make_ray_dir(float dx, float dy, float dz) {
+    RayDir r;
+    r.dx = dx; r.dy = dy; r.dz = dz;
+    r.rdx = __frcp_rn(dx); r.rdy = __frcp_rn(dy); r.rdz = __frcp_rn(dz);
+    r.sx = copysignf(1.0f, dx); r.sy = copysignf(1.0f, dy); r.sz = copysignf(1.0f, dz);
+    return r;
+}
+
+// ONE trip of the reference's marching loop body (raymarching.cu:754-812), precondition t < far: probes the cell under
+// the ray at t.  Occupied: returns true with the sample (x, y, z, dt, delta_t = t_new - last_t) and t advanced by dt.
+// Empty: returns false with t advanced, in dt increments, past the cell's exit.  The loop state is just (t, last_t), so a
+// caller may interleave the probes of 32 rays in lockstep (the persistent renderer) or run them to completion (march_ray).
+__device__ __forceinline__ bool march_probe(const MarchConst &m, float ox, float oy, float oz, const RayDir &rd, float &t, float &last_t,
+                                            float &x, float &y, float &z, float &dt, float &delta_t) {
+    const bool one_level = m.cm1f == 0.0f;     // cascade 1 (bound <= 1): the mip level is always 0
+    const bool const_dt = m.dt_gamma == 0.0f;  // dt = clamp(t * 0, dt_min, dt_max) for every t (NaN-safe: fmaxf drops the NaN)
+    const float dt0 = fminf(m.dt_max, fmaxf(m.dt_min, 0.0f));
+    x = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(rd.dx, t, ox)));
+    y = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(rd.dy, t, oy)));
+    z = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(rd.dz, t, oz)));
+    dt = const_dt ? dt0 : march_dt(t, m);
+    int level = 0;
+    if (!one_level) {
+        const int l_pos = mip_level(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), m.cm1f);
+        const int l_dt = mip_level(__fmul_rn(__fmul_rn(dt, m.Hf), 0.5f), m.cm1f);
+        level = max(l_pos, l_dt);
+    }
+    const float mip_bound = m.mip_b[level];
+    const float mip_rbound = m.mip_rb[level];
+    const int nx = cell_coord(x, mip_rbound, m);
+    const int ny = cell_coord(y, mip_rbound, m);
+    const int nz = cell_coord(z, mip_rbound, m);
+    const uint32_t idx = (uint32_t)__fmaf_rn(m.H3f, (float)level, (float)morton3d(nx, ny, nz));
+    const bool occ = (__ldg(m.grid + (idx >> 3)) >> (idx & 7)) & 1;
+    if (occ) {
+        t = __fadd_rn(t, dt);
+        delta_t = __fsub_rn(t, last_t);
+        last_t = t;
+        return true;
+    }
+    const float tx = cell_exit(nx, rd.sx, mip_bound, x, rd.rdx, m);
+    const float ty = cell_exit(ny, rd.sy, mip_bound, y, rd.rdy, m);
+    const float tz = cell_exit(nz, rd.sz, mip_bound, z, rd.rdz, m);
+    const float tt = __fadd_rn(t, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+    if (const_dt) {
+        do { t = __fadd_rn(t, dt0); } while (t < tt);
+    } else {
+        do { t = __fadd_rn(t, march_dt(t, m)); } while (t < tt);
+    }
+    return false;
+}
+
+// Marches one ray from t for up to n_step occupied samples (one reference chunk).  emit(step, x, y, z, dt, delta_t) is
+// called per sample.  Returns the number of samples emitted.
 template <class Emit>
 __device__ __forceinline__ uint32_t march_ray(const MarchConst &m, float ox, float oy, float oz, float dx, float dy,
                                               float dz, float t, float far, uint32_t n_step, Emit &&emit) {
-    const float rdx = __frcp_rn(dx), rdy = __frcp_rn(dy), rdz = __frcp_rn(dz);
-    const float sx = copysignf(1.0f, dx), sy = copysignf(1.0f, dy), sz = copysignf(1.0f, dz);
+    const RayDir rd = make_ray_dir(dx, dy, dz);
     uint32_t step = 0;
-    float last_t = t;
+    float last_t = t, x, y, z, dt, delta_t;
     while (t < far && step < n_step) {
-        const float x = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(dx, t, ox)));
-        const float y = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(dy, t, oy)));
-        const float z = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(dz, t, oz)));
-        const float dt = march_dt(t, m);
-        const int l_pos = mip_level(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), m.cm1f);
-        const int l_dt = mip_level(__fmul_rn(__fmul_rn(dt, m.Hf), 0.5f), m.cm1f);
-        const int level = max(l_pos, l_dt);
-        const float mip_bound = fminf((float)(1 << level), m.bound);
-        const float mip_rbound = __frcp_rn(mip_bound);
-        const int nx = cell_coord(x, mip_rbound, m);
-        const int ny = cell_coord(y, mip_rbound, m);
-        const int nz = cell_coord(z, mip_rbound, m);
-        const uint32_t idx = (uint32_t)__fmaf_rn(m.H3f, (float)level, (float)morton3d(nx, ny, nz));
-        const bool occ = (__ldg(m.grid + (idx >> 3)) >> (idx & 7)) & 1;
-        if (occ) {
-            t = __fadd_rn(t, dt);
-            emit(step, x, y, z, dt, __fsub_rn(t, last_t));
-            last_t = t;
+        if (march_probe(m, ox, oy, oz, rd, t, last_t, x, y, z, dt, delta_t)) {
+            emit(step, x, y, z, dt, delta_t);
             step++;
-        } else {
-            const float tx = cell_exit(nx, sx, mip_bound, x, rdx, m);
-            const float ty = cell_exit(ny, sy, mip_bound, y, rdy, m);
-            const float tz = cell_exit(nz, sz, mip_bound, z, rdz, m);
-            const float tt = __fadd_rn(t, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
-            do {
-                t = __fadd_rn(t, march_dt(t, m));
-            } while (t < tt);
         }
     }
     return step;
@@ -213,6 +256,28 @@ __device__ __forceinline__ uint32_t grid_row_fast(const LevelConst &lc, uint32_t
     if (lc.mode == 3) return (x + (y + z * lc.stride) * lc.stride) % lc.size;
     const uint32_t h = hash3(x, y, z);
     return lc.mode == 1 ? (h & (lc.size - 1)) : (h % lc.size);
+}
+
+// The 8 table rows of the cell whose low corner is (g0, g1, g2); corner k = (k & 1, (k >> 1) & 1, (k >> 2) & 1), the order
+// the reference accumulates in (gridencoder.cu:146-171).  lc.mode is uniform per level, so the branch never diverges, and the
+// two common modes share the per-axis terms between corners instead of recomputing the hash / dense index 8 times.
+__device__ __forceinline__ void cell_rows(const LevelConst &lc, uint32_t g0, uint32_t g1, uint32_t g2, uint32_t (&row)[8]) {
+    if (lc.mode == 1) {            // hashed level, power-of-two table: (x ^ y*P1 ^ z*P2) & (T - 1); (g+1)*P = g*P + P mod 2^32
+        const uint32_t m = lc.size - 1u;
+        const uint32_t x0 = g0, x1 = g0 + 1u;
+        const uint32_t y0 = g1 * 2654435761u, y1 = y0 + 2654435761u;
+        const uint32_t z0 = g2 * 805459861u, z1 = z0 + 805459861u;
+        row[0] = (x0 ^ y0 ^ z0) & m; row[1] = (x1 ^ y0 ^ z0) & m; row[2] = (x0 ^ y1 ^ z0) & m; row[3] = (x1 ^ y1 ^ z0) & m;
+        row[4] = (x0 ^ y0 ^ z1) & m; row[5] = (x1 ^ y0 ^ z1) & m; row[6] = (x0 ^ y1 ^ z1) & m; row[7] = (x1 ^ y1 ^ z1) & m;
+    } else if (lc.mode == 0) {     // dense level that fits its table: x + y*s + z*s*s
+        const uint32_t s1 = lc.stride, s2 = s1 * s1;
+        const uint32_t b = g0 + (g1 + g2 * s1) * s1;
+        row[0] = b; row[1] = b + 1u; row[2] = b + s1; row[3] = b + s1 + 1u;
+        row[4] = b + s2; row[5] = b + s2 + 1u; row[6] = b + s2 + s1; row[7] = b + s2 + s1 + 1u;
+    } else {                       // non-power-of-two hash table or wrapped dense level: the general form
+#pragma unroll
+        for (int k = 0; k < 8; k++) row[k] = grid_row_fast(lc, g0 + (k & 1), g1 + ((k >> 1) & 1), g2 + ((k >> 2) & 1));
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -2,20 +2,16 @@
 //   ngp_network_forward : hash-grid encode -> sigma MLP -> SH -> colour MLP -> exp/sigmoid, one kernel, nothing but
 //                         xyz/dir in and sigma/rgb out touches HBM        (nerf/network_ff.py:51-74)
 //   ngp_render          : NeRFRenderer.run_cuda's whole inference loop (nerf/renderer.py:261-284,329-386) as ONE
-//                         persistent cooperative launch: per iteration every CTA pulls 128-sample tiles
-//                         {march -> encode -> MLPs -> composite -> stable compaction (decoupled look-back)} and the
-//                         grid meets at one grid-wide barrier, because the reference's `n_step = clamp(N // n_alive, 1, 8)`
-//                         schedule is global and the per-ray sample counts (an integer output we must match) depend on it.
-//
-// Tile anatomy (128 threads = 4 warps, 128 sample rows, <= 56 KB smem so 4 CTAs share an SM):
-//   phase A  thread r <-> ray r of the tile: occupancy-bitfield DDA, emits <= n_step samples into smem rows
-//   phase B  thread r <-> sample row r: 16 levels x 8 corners of half2 gathers (32 in flight), trilinear blend in
-//            fp32, row written as fp16 into the A-operand staging buffer
-//   phase C  warp w <-> rows 32w..32w+31: 7 dense layers on tensor cores, fp32 accumulate, activations chained in
-//            registers (accumulator fragment == next A fragment), weights read from smem in B-fragment order
-//   phase D  thread r <-> ray r: front-to-back compositing in registers, early termination, survivor ballot
+//                         persistent cooperative launch, one 16-warp CTA per SM.  Warps are autonomous: a warp pulls a
+//                         group of 32 live rays and, per sample, runs {march_one -> hash-grid gather -> both MLPs on
+//                         tensor cores -> composite} with lane r owning ray r / row r; nothing but o/d in and the ray
+//                         accumulators out touches HBM.  The grid meets once per iteration because the reference's
+//                         `n_step = clamp(N // n_alive, 1, 8)` schedule is global and the per-ray sample counts (an
+//                         integer output we must match) depend on it.
 #include <cooperative_groups.h>
 #include <float.h>
+#include <stddef.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "device_math.cuh"
@@ -39,9 +35,9 @@ struct NetConst {
 };
 
 struct RenderCtr {
-    uint32_t n_alive[2];
+    uint32_t n_alive[3];
     uint32_t ticket[3];
-    uint32_t iters;
+    uint32_t cursor, max_rounds;
     unsigned long long samples;
     unsigned long long tiles;
 };
@@ -64,33 +60,38 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
         dst[0] = dst[1] = dst[2] = dst[3] = make_uint4(0, 0, 0, 0);
         return;
     }
-#pragma unroll
+    // 4 levels (32 independent 4-byte gathers) per trip; the trip loop is deliberately NOT unrolled: the renderer's 16 warps
+    // sit in different phases, and a 4x smaller gather body keeps them inside the instruction cache
+#pragma unroll 1
     for (int grp = 0; grp < 4; grp++) {
         float f[4][3];
         __half2 v[4][8];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const LevelConst lc = nc.lv[grp * 4 + j];
-            float p0 = __fmaf_rn(u0, lc.scale, 0.5f), p1 = __fmaf_rn(u1, lc.scale, 0.5f), p2 = __fmaf_rn(u2, lc.scale, 0.5f);
+            const LevelConst &lc = nc.lv[grp * 4 + j];
+            const float scale = lc.scale;
+            float p0 = __fmaf_rn(u0, scale, 0.5f), p1 = __fmaf_rn(u1, scale, 0.5f), p2 = __fmaf_rn(u2, scale, 0.5f);
             const uint32_t g0 = (uint32_t)floorf(p0), g1 = (uint32_t)floorf(p1), g2 = (uint32_t)floorf(p2);
             f[j][0] = __fsub_rn(p0, (float)g0); f[j][1] = __fsub_rn(p1, (float)g1); f[j][2] = __fsub_rn(p2, (float)g2);
             const __half2 *tl = nc.table + lc.offset;
+            uint32_t row[8];
+            cell_rows(lc, g0, g1, g2, row);
 #pragma unroll
-            for (int k = 0; k < 8; k++)
-                v[j][k] = __ldg(tl + grid_row_fast(lc, g0 + (k & 1), g1 + ((k >> 1) & 1), g2 + ((k >> 2) & 1)));
+            for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
         }
         uint32_t packed[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
             const float q0 = 1.0f - p0, q1 = 1.0f - p1, q2 = 1.0f - p2;
+            const float w00 = q0 * q1, w10 = p0 * q1, w01 = q0 * p1, w11 = p0 * p1;   // (w_x * w_y) * w_z, gridencoder.cu:148-160
+            const float w[8] = {w00 * q2, w10 * q2, w01 * q2, w11 * q2, w00 * p2, w10 * p2, w01 * p2, w11 * p2};
             float a0 = 0.f, a1 = 0.f;
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-                const float w = ((k & 1) ? p0 : q0) * ((k & 2) ? p1 : q1) * ((k & 4) ? p2 : q2);
                 const float2 g = __half22float2(v[j][k]);
-                a0 = fmaf(w, g.x, a0);
-                a1 = fmaf(w, g.y, a1);
+                a0 = fmaf(w[k], g.x, a0);
+                a1 = fmaf(w[k], g.y, a1);
             }
             packed[j] = pack_half2(a0, a1);
         }
@@ -112,8 +113,9 @@ __device__ __forceinline__ float round_half(float v) { return __half2float(__flo
 //   s_enc / s_sh : staged fp16 inputs.   emit(row, sigma, r, g, b) is called by the lane that owns the value pair.
 // dtype flow as in the reference under autocast: sigma_net output is half; sigma = exp(float(h0)) * density_scale;
 // colour input = [SH16 (half), geo15 (half), 0]; rgb = half(sigmoid(float(half(h))))   (network_ff.py:56-72).
-template <class EmitSigma, class EmitRgb>
-__device__ __forceinline__ void mlp_rows32(const NetConst &nc, const uint2 *__restrict__ s_w, const __half *s_enc, const __half *s_sh,
+//   sh_row(r)    : staged SH row (16 halves) of sample row r -- per row in the network kernel, per RAY in the renderer.
+template <class ShRow, class EmitSigma, class EmitRgb>
+__device__ __forceinline__ void mlp_rows32(const NetConst &nc, const uint2 *__restrict__ s_w, const __half *s_enc, ShRow &&sh_row,
                                            int row0, int lane, EmitSigma &&emit_sigma, EmitRgb &&emit_rgb) {
     const int g = lane >> 2, t = lane & 3;
     const uint2 *w_s0 = s_w;                                   // [64][32]
@@ -149,8 +151,8 @@ __device__ __forceinline__ void mlp_rows32(const NetConst &nc, const uint2 *__re
     // forced to zero; the packed first-layer weights carry the matching column shift.
 #pragma unroll
     for (int mt = 0; mt < 2; mt++) {
-        const uint32_t *lo = reinterpret_cast<const uint32_t *>(s_sh + (row0 + mt * 16 + g) * kShStride);
-        const uint32_t *hi = reinterpret_cast<const uint32_t *>(s_sh + (row0 + mt * 16 + g + 8) * kShStride);
+        const uint32_t *lo = reinterpret_cast<const uint32_t *>(sh_row(row0 + mt * 16 + g));
+        const uint32_t *hi = reinterpret_cast<const uint32_t *>(sh_row(row0 + mt * 16 + g + 8));
         A0[mt][0][0] = lo[t]; A0[mt][0][1] = hi[t]; A0[mt][0][2] = lo[4 + t]; A0[mt][0][3] = hi[4 + t];
         uint32_t g0 = pack_half2(O[mt][0][0], O[mt][0][1]), g1 = pack_half2(O[mt][0][2], O[mt][0][3]);
         if (t == 0) {
@@ -223,7 +225,7 @@ k_network_forward(NetConst nc, const float *__restrict__ xyzs, const float *__re
         }
         __syncwarp();
         const uint32_t base = tile * kTile;
-        mlp_rows32(nc, s_w, s_enc, s_sh, warp * 32, lane,
+        mlp_rows32(nc, s_w, s_enc, [&](int r) { return s_sh + r * kShStride; }, warp * 32, lane,
                    [&](int r, float s) { if (base + r < M) sigmas[base + r] = s; },
                    [&](int r, int t, float a, float b) {
                        if (base + r < M) {
@@ -236,38 +238,170 @@ k_network_forward(NetConst nc, const float *__restrict__ xyzs, const float *__re
 }
 
 // ---------------------------------------------------------------------------------------------- persistent renderer
+// Warp-autonomous design: one CTA of 16 warps per SM and NO block-level barrier after the prologue.  Lane r of a warp owns
+// ray r of the warp's current group and that ray's accumulators.  One "chunk" (= one reference loop iteration for those rays):
+//   march     every lane marches its ray for up to n_step samples (registers -> per-warp smem records, raymarching.cu:706-814)
+//   evaluate  the warp's samples, densely packed ray-major (so consecutive rows are consecutive samples of one ray and share
+//             hash-grid cells), go through {16-level gather -> sigma MLP -> SH + colour MLP} 32 rows at a time on tensor cores
+//   composite every lane accumulates its own samples front to back in registers with early termination (:828-913)
+// so xyz / dirs / deltas / sigmas / rgbs never exist in global memory.  Latency is hidden by the other 15 warps of the SM being
+// in other phases of their own chunks.
+//
+// Schedule.  `n_step = clamp(N // n_alive, 1, 8)` (renderer.py:357) is global, and the per-ray chunking is visible in the
+// results (rays_t restarts from the compositor's sum of deltas at every chunk boundary), so:
+//   phase A  while n_step < 8: one grid-wide barrier per iteration; warps pull 32-ray groups from an atomic ticket and append
+//            survivors to the next live list with one ballot + one atomicAdd per warp (list order is not the reference's,
+//            which no per-ray output depends on; the stand-alone compact_alive op keeps the stable order);
+//   phase B  once n_alive <= N / 8 the schedule is locked at 8 for good (n_alive never grows), so every ray's remaining
+//            chunking is known: warps keep their rays in registers chunk after chunk, refill dead lanes from the live list,
+//            and the grid does not meet again until the epilogue.  Per-ray results are identical to the iteration-synchronous
+//            loop; iterations = phase-A iterations + the longest phase-B ray.
+constexpr int kRenderThreads = 512;
+constexpr int kRenderWarps = kRenderThreads / 32;
+constexpr int kMaxStep = 8;                    // renderer.py:357
+constexpr int kSlotStride = kMaxStep + 1;      // lane-major sample slots, odd stride => conflict-free for lane- and row-order access
+constexpr int kSlots = 32 * kSlotStride;
+
+struct WarpSmem {
+    float x[kSlots], y[kSlots], z[kSlots];     // sample position; after the MLPs: sigma, half2(r, g) bits, b
+    float dt[kSlots], dl[kSlots];              // deltas[:, 0], deltas[:, 1]
+    float ray[6 * 32];                         // [k][lane]: origin and direction of the lane's ray
+    uint16_t rowmap[32 * kMaxStep];            // dense sample row -> (lane << 4) | s
+    __half enc[32 * kEncStride];               // A-operand staging of the current 32 rows; first 16 B of a row = (sigma, r, g, b) after the MLPs
+    __half sh[32 * kShStride];                 // degree-4 SH of lane r's ray direction
+};
+static_assert(sizeof(WarpSmem) % 16 == 0 && offsetof(WarpSmem, enc) % 16 == 0 && offsetof(WarpSmem, sh) % 16 == 0, "WarpSmem alignment");
+
 struct RenderArgs {
     const float *rays_o, *rays_d;
     uint32_t N;
     float min_near, bg_color;
-    uint32_t max_steps;
+    uint32_t max_steps, lock_schedule;
+    int march_budget;
     float aabb[6];
     MarchConst mc;
     float *nears, *fars, *rays_t;
     int *alive[2];
-    unsigned long long *status;
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
     long long *stats;
+    long long *prof;   // optional [8]: warp-cycles per phase (diagnostics, ngp_ctx_phase_cycles)
 };
 
-__global__ void __launch_bounds__(kTile, 4) k_render(NetConst nc, RenderArgs ra) {
+// One PASS of a warp over its 32 ray slots.  Every marching lane advances its ray by at most `march_budget` cell probes
+// towards the n_step samples of its current chunk (time-slicing: a lane crossing a long empty stretch spends several passes
+// on it while its neighbours keep producing samples); the samples produced in this pass are evaluated, densely packed
+// ray-major, 32 rows at a time, and composited by their own lanes.  Chunk semantics (raymarching.cu:706-814, 828-913) are kept
+// by the caller: `emitted` counts the chunk's samples so far, `exhausted` = the marcher reached `far`, `terminated` = T < 1e-4.
+template <bool kProf>
+__device__ __forceinline__ void warp_pass(const NetConst &nc, const RenderArgs &ra, const uint2 *__restrict__ s_w, WarpSmem &ws, int lane,
+                                          bool marching, uint32_t n_step, float &tm, float &last_t, float far, RayAcc &a, uint32_t &emitted,
+                                          bool &terminated, bool &exhausted, long long (&pc)[8]) {
+    uint32_t produced = 0;
+    long long c0 = kProf ? clock64() : 0, c1;
+#define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
+    {
+        const float ox = ws.ray[lane], oy = ws.ray[32 + lane], oz = ws.ray[64 + lane];
+        const RayDir rd = make_ray_dir(ws.ray[96 + lane], ws.ray[128 + lane], ws.ray[160 + lane]);
+        float x, y, z, dt, dl;
+        // lockstep: every lane probes one cell per trip, so the warp stays converged whatever mix of occupied / empty
+        // cells its 32 rays are crossing (a per-lane `while` would leave the few lanes in empty space running alone)
+        for (int p = 0; p < ra.march_budget; p++) {
+            const bool go = marching && emitted < n_step && tm < far;
+            if (!__any_sync(0xffffffffu, go)) break;
+            if (go && march_probe(ra.mc, ox, oy, oz, rd, tm, last_t, x, y, z, dt, dl)) {
+                if (!terminated) {   // after T-termination the rest of the chunk is only counted (samples_per_ray parity)
+                    const int slot = lane * kSlotStride + (int)produced;
+                    ws.x[slot] = x; ws.y[slot] = y; ws.z[slot] = z; ws.dt[slot] = dt; ws.dl[slot] = dl;
+                    produced++;
+                }
+                emitted++;
+            }
+        }
+        if (marching) exhausted = emitted < n_step && !(tm < far);
+    }
+    NGP_PROF(1)
+    const uint32_t incl = warp_inclusive_sum(produced, lane);
+    const uint32_t base = incl - produced, total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    for (uint32_t s = 0; s < produced; s++) ws.rowmap[base + s] = (uint16_t)((lane << 4) | s);
+    __syncwarp();
+    NGP_PROF(2)
+    for (uint32_t row0 = 0; row0 < total; row0 += 32) {
+        const uint32_t row = row0 + lane;
+        const bool valid = row < total;
+        int slot = 0;
+        if (valid) {
+            const uint32_t m = ws.rowmap[row];
+            slot = (int)(m >> 4) * kSlotStride + (int)(m & 15u);
+            encode_point(nc, ws.x[slot], ws.y[slot], ws.z[slot], reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
+        }
+        __syncwarp();
+        NGP_PROF(3)
+        mlp_rows32(nc, s_w, ws.enc,
+                   [&](int r) {
+                       const uint32_t rr = row0 + (uint32_t)r;
+                       const uint32_t ln = rr < total ? (uint32_t)(ws.rowmap[rr] >> 4) : 0u;
+                       return ws.sh + ln * kShStride;
+                   },
+                   0, lane, [&](int r, float sg) { reinterpret_cast<float *>(ws.enc + r * kEncStride)[0] = sg; },
+                   [&](int r, int t, float c0, float c1) {
+                       float *o = reinterpret_cast<float *>(ws.enc + r * kEncStride);
+                       if (t == 0) { o[1] = c0; o[2] = c1; } else { o[3] = c0; }
+                   });
+        __syncwarp();
+        NGP_PROF(4)
+        if (valid) {
+            const float4 o = *reinterpret_cast<const float4 *>(ws.enc + lane * kEncStride);
+            ws.x[slot] = o.x; ws.y[slot] = __uint_as_float(pack_half2(o.y, o.z)); ws.z[slot] = o.w;   // rgb are half-rounded: exact
+        }
+    }
+    __syncwarp();
+    for (uint32_t s = 0; s < produced; s++) {
+        const int slot = lane * kSlotStride + (int)s;
+        const uint32_t rg = __float_as_uint(ws.y[slot]);
+        const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&rg));
+        if (composite_sample(a, ws.x[slot], c.x, c.y, ws.z[slot], ws.dt[slot], ws.dl[slot])) { terminated = true; break; }
+    }
+    __syncwarp();   // the records are rewritten by the next pass
+    NGP_PROF(5)
+#undef NGP_PROF
+}
+
+__device__ __forceinline__ void load_ray(const RenderArgs &ra, WarpSmem &ws, int lane, int index, float &tm, float &last_t, float &far, RayAcc &a) {
+    const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
+    const float dx = __ldg(d), dy = __ldg(d + 1), dz = __ldg(d + 2);
+    ws.ray[lane] = __ldg(o); ws.ray[32 + lane] = __ldg(o + 1); ws.ray[64 + lane] = __ldg(o + 2);
+    ws.ray[96 + lane] = dx; ws.ray[128 + lane] = dy; ws.ray[160 + lane] = dz;
+    uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + lane * kShStride);
+    sh_to_half(dx, dy, dz, srow[0], srow[1]);   // the direction is constant along the ray
+    tm = __ldcg(ra.rays_t + index);
+    last_t = tm;
+    far = __ldcg(ra.fars + index);
+    a.t = tm; a.ws = __ldcg(ra.weights_sum + index); a.d = __ldcg(ra.depth + index);
+    a.r = __ldcg(ra.image + (size_t)index * 3); a.g = __ldcg(ra.image + (size_t)index * 3 + 1); a.b = __ldcg(ra.image + (size_t)index * 3 + 2);
+}
+
+__device__ __forceinline__ void store_ray(const RenderArgs &ra, int index, const RayAcc &a, bool survives) {
+    if (survives) __stcg(ra.rays_t + index, a.t);                       // raymarching.cu:905-911
+    __stcg(ra.weights_sum + index, a.ws); __stcg(ra.depth + index, a.d);
+    __stcg(ra.image + (size_t)index * 3, a.r); __stcg(ra.image + (size_t)index * 3 + 1, a.g); __stcg(ra.image + (size_t)index * 3 + 2, a.b);
+}
+
+template <bool kProf>
+__global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, RenderArgs ra) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint2 *s_w = reinterpret_cast<uint2 *>(smem_raw);
-    __half *s_enc = reinterpret_cast<__half *>(s_w + nc.wpack_count);
-    __half *s_sh = s_enc + kTile * kEncStride;
-    float *s_xyz = reinterpret_cast<float *>(s_sh + kTile * kShStride);
-    float *s_dt = s_xyz + kTile * 3;
-    float *s_dlt = s_dt + kTile;
-    __shared__ uint32_t s_tile, s_base, s_wcnt[kTile / 32], s_emit[kTile / 32];
-
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    WarpSmem &ws = reinterpret_cast<WarpSmem *>(s_w + nc.wpack_count)[warp];
     const uint32_t N = ra.N;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const bool counting = ra.samples_per_ray != nullptr || ra.stats != nullptr;
     copy_wpack_to_smem(nc, s_w);
 
-    // ---- prologue: near/far, ray state, first alive list (renderer.py:273-274, 335-343)
+    // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
         const float *o = ra.rays_o + (size_t)n * 3, *d = ra.rays_d + (size_t)n * 3;
         float near, far;
@@ -279,153 +413,131 @@ __global__ void __launch_bounds__(kTile, 4) k_render(NetConst nc, RenderArgs ra)
         ra.image[(size_t)n * 3] = 0.f; ra.image[(size_t)n * 3 + 1] = 0.f; ra.image[(size_t)n * 3 + 2] = 0.f;
         if (ra.samples_per_ray) ra.samples_per_ray[n] = 0;
     }
-    if (blockIdx.x == 0 && tid == 0) ra.ctr->n_alive[0] = N;
+    if (blockIdx.x == 0 && tid == 0) ra.ctr->n_alive[0] = N;   // all counters were zeroed by the host before the launch
     grid.sync();
 
-    uint32_t step = 0, iter = 0, cur = 0;
+    uint32_t step = 0, iter = 0, tot_emitted = 0, passes = 0, max_rounds = 0;
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long k_start = kProf ? clock64() : 0;
+    // One trip of this loop = one reference iteration (phase A, grid barrier at its end) or, once the schedule is locked at
+    // n_step = 8, the whole rest of the frame (phase B, rays stay in their lanes chunk after chunk).
     while (step < ra.max_steps) {
-        const uint32_t n_alive = __ldcg(&ra.ctr->n_alive[cur]);
+        const uint32_t n_alive = __ldcg(&ra.ctr->n_alive[iter % 3]);
         if (n_alive == 0) break;
         uint32_t n_step = N / n_alive;                                  // renderer.py:357
-        n_step = n_step > 8 ? 8 : (n_step < 1 ? 1 : n_step);
-        const uint32_t TR = kTile / n_step;                             // rays per tile
-        const uint32_t n_tiles = (n_alive + TR - 1) / TR;
-        const int *alive_in = ra.alive[cur];
-        int *alive_out = ra.alive[cur ^ 1];
-        uint32_t *ticket = &ra.ctr->ticket[iter % 3];
-        if (blockIdx.x == 0 && tid == 0) ra.ctr->ticket[(iter + 1) % 3] = 0;
-
-        for (;;) {
-            if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-            // rows no ray writes must read as "no sample"
-            s_dt[tid] = 0.f;
-            {
-                uint4 *srow = reinterpret_cast<uint4 *>(s_sh + tid * kShStride);
-                srow[0] = srow[1] = make_uint4(0, 0, 0, 0);
-            }
-            __syncthreads();
-            const uint32_t tile = s_tile;
-            if (tile >= n_tiles) break;
-
-            // ---- phase A: march (raymarching.cu:706-814)
-            const uint32_t n = tile * TR + tid;
-            const bool has_ray = (uint32_t)tid < TR && n < n_alive;
-            int index = -1;
-            uint32_t emitted = 0;
-            if (has_ray) {
-                index = __ldcg(alive_in + n);
-                const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
-                const float dx = __ldg(d), dy = __ldg(d + 1), dz = __ldg(d + 2);
-                const uint32_t r0 = tid * n_step;
-                emitted = march_ray(ra.mc, __ldg(o), __ldg(o + 1), __ldg(o + 2), dx, dy, dz, __ldcg(ra.rays_t + index), __ldcg(ra.fars + index), n_step,
-                                    [&](uint32_t s, float x, float y, float z, float dt, float delta_t) {
-                                        const uint32_t r = r0 + s;
-                                        s_xyz[r * 3] = x; s_xyz[r * 3 + 1] = y; s_xyz[r * 3 + 2] = z;
-                                        s_dt[r] = dt; s_dlt[r] = delta_t;
-                                    });
-                if (emitted) {
-                    uint4 lo, hi;
-                    sh_to_half(dx, dy, dz, lo, hi);
-                    for (uint32_t s = 0; s < emitted; s++) {
-                        uint4 *srow = reinterpret_cast<uint4 *>(s_sh + (r0 + s) * kShStride);
-                        srow[0] = lo; srow[1] = hi;
-                    }
-                }
-            }
-            __syncthreads();
-
-            // ---- phase B: hash-grid gather for sample row `tid`
-            {
-                uint4 *erow = reinterpret_cast<uint4 *>(s_enc + tid * kEncStride);
-                if (s_dt[tid] != 0.f) encode_point(nc, s_xyz[tid * 3], s_xyz[tid * 3 + 1], s_xyz[tid * 3 + 2], erow);
-                else erow[0] = erow[1] = erow[2] = erow[3] = make_uint4(0, 0, 0, 0);
-            }
-            __syncwarp();
-
-            // ---- phase C: both MLPs on tensor cores; (sigma, r, g, b) overwrite the first 16 bytes of the warp's own rows
-            {
-                // a warp skips the MLP when none of its 32 rows holds a sample
-                const bool any = __any_sync(0xffffffffu, s_dt[tid] != 0.f);
-                if (any) {
-                    mlp_rows32(nc, s_w, s_enc, s_sh, warp * 32, lane,
-                               [&](int r, float s) { reinterpret_cast<float *>(s_enc + r * kEncStride)[0] = s; },
-                               [&](int r, int t, float a, float b) {
-                                   float *o = reinterpret_cast<float *>(s_enc + r * kEncStride);
-                                   if (t == 0) { o[1] = a; o[2] = b; } else { o[3] = a; }
-                               });
-                }
-            }
-            __syncthreads();
-
-            // ---- phase D: composite (raymarching.cu:828-913) + survivor flag
-            bool survives = false;
-            if (has_ray) {
-                RayAcc a;
-                a.t = __ldcg(ra.rays_t + index); a.ws = __ldcg(ra.weights_sum + index); a.d = __ldcg(ra.depth + index);
-                a.r = __ldcg(ra.image + (size_t)index * 3); a.g = __ldcg(ra.image + (size_t)index * 3 + 1); a.b = __ldcg(ra.image + (size_t)index * 3 + 2);
-                uint32_t s = 0;
-                const uint32_t r0 = tid * n_step;
-                while (s < n_step) {
-                    const float dt = s_dt[r0 + s];
-                    if (dt == 0.f) break;
-                    const float4 o = *reinterpret_cast<const float4 *>(s_enc + (r0 + s) * kEncStride);
-                    if (composite_sample(a, o.x, o.y, o.z, o.w, dt, s_dlt[r0 + s])) break;
-                    s++;
-                }
-                survives = (s == n_step);
-                if (survives) __stcg(ra.rays_t + index, a.t);
-                __stcg(ra.weights_sum + index, a.ws); __stcg(ra.depth + index, a.d);
-                __stcg(ra.image + (size_t)index * 3, a.r); __stcg(ra.image + (size_t)index * 3 + 1, a.g); __stcg(ra.image + (size_t)index * 3 + 2, a.b);
-                if (ra.samples_per_ray && emitted) __stcg(ra.samples_per_ray + index, __ldcg(ra.samples_per_ray + index) + (int)emitted);
-            }
-            // ---- stable compaction of survivors (renderer.py:369) : ballot -> block offsets -> look-back across tiles
-            const uint32_t ballot = __ballot_sync(0xffffffffu, survives);
-            const uint32_t wemit = warp_sum(emitted);
-            if (lane == 0) { s_wcnt[warp] = __popc(ballot); s_emit[warp] = wemit; }
-            __syncthreads();
-            uint32_t woff = 0, total = 0;
-#pragma unroll
-            for (int w = 0; w < kTile / 32; w++) {
-                const uint32_t c = s_wcnt[w];
-                woff += (w < warp) ? c : 0;
-                total += c;
-            }
-            if (warp == 0) {
-                const uint32_t base = lookback_exclusive_prefix(ra.status, tile, total, iter + 1, lane);
-                if (lane == 0) {
-                    s_base = base;
-                    if (tile == n_tiles - 1) __stcg(&ra.ctr->n_alive[cur ^ 1], base + total);
-                    if (ra.stats) {
-                        atomicAdd(&ra.ctr->samples, (unsigned long long)(s_emit[0] + s_emit[1] + s_emit[2] + s_emit[3]));
-                        atomicAdd(&ra.ctr->tiles, 1ull);
-                    }
-                }
-            }
-            __syncthreads();
-            if (survives) __stcg(alive_out + s_base + woff + __popc(ballot & ((1u << lane) - 1u)), index);
-            __syncthreads();   // smem is reused by the next tile
+        n_step = n_step > kMaxStep ? kMaxStep : (n_step < 1 ? 1 : n_step);
+        const bool locked = n_step == kMaxStep && ra.lock_schedule;     // n_alive never grows => n_step stays 8 for good
+        const int *alive_in = ra.alive[iter & 1];
+        int *alive_out = ra.alive[(iter & 1) ^ 1];
+        uint32_t *cursor = &ra.ctr->ticket[iter % 3];
+        uint32_t *next_count = &ra.ctr->n_alive[(iter + 1) % 3];
+        if (blockIdx.x == 0 && tid == 0) {   // neither word is touched by anyone else during this iteration
+            ra.ctr->ticket[(iter + 1) % 3] = 0;
+            ra.ctr->n_alive[(iter + 2) % 3] = 0;
         }
-        grid.sync();
+
+        bool has_ray = false, list_done = false, terminated = false, exhausted = false;
+        int index = 0, spr = 0;
+        float tm = 0.f, last_t = 0.f, far = 0.f;
+        RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        uint32_t emitted = 0, ray_step = 0, rounds = 0;
+        for (;;) {
+            // ---- refill free lanes from the live list (one atomic per warp)
+            const uint32_t need = __ballot_sync(0xffffffffu, !has_ray);
+            if (need && !list_done) {
+                const uint32_t cnt = (uint32_t)__popc(need);
+                uint32_t start = 0;
+                if (lane == 0) start = atomicAdd(cursor, cnt);
+                start = __shfl_sync(0xffffffffu, start, 0);
+                if (!has_ray) {
+                    const uint32_t my = start + (uint32_t)__popc(need & lt_mask);
+                    if (my < n_alive) {
+                        index = __ldcg(alive_in + my);
+                        load_ray(ra, ws, lane, index, tm, last_t, far, a);
+                        has_ray = true; terminated = false; exhausted = false;
+                        emitted = 0; ray_step = step; rounds = 1; spr = 0;
+                    }
+                }
+                list_done = start + cnt >= n_alive;
+            }
+            if (!__any_sync(0xffffffffu, has_ray)) break;
+
+            warp_pass<kProf>(nc, ra, s_w, ws, lane, has_ray, n_step, tm, last_t, far, a, emitted, terminated, exhausted, pc);
+            passes++;
+
+            // ---- chunk bookkeeping (renderer.py:347-373)
+            const bool chunk_done = has_ray && (exhausted || emitted == n_step || (terminated && !counting));
+            bool survives = chunk_done && !terminated && !exhausted;
+            bool retire = chunk_done;
+            if (chunk_done) {
+                tot_emitted += emitted;
+                spr += (int)emitted;
+                if (locked && survives && ray_step + kMaxStep < ra.max_steps) {
+                    // next reference iteration for this ray, without leaving the lane: the marcher restarts from the
+                    // compositor's t (rays_t, raymarching.cu:905) exactly as the reference's next march_rays call does
+                    ray_step += kMaxStep; rounds++;
+                    tm = a.t; last_t = tm; emitted = 0;
+                    retire = false;
+                }
+            }
+            if (retire) {
+                store_ray(ra, index, a, survives);
+                if (ra.samples_per_ray && spr) ra.samples_per_ray[index] += spr;
+                max_rounds = max(max_rounds, rounds);
+                has_ray = false;
+            }
+            if (!locked) {                                               // renderer.py:369
+                const uint32_t ballot = __ballot_sync(0xffffffffu, retire && survives);
+                if (ballot) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(next_count, (uint32_t)__popc(ballot));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (retire && survives) __stcg(alive_out + base + __popc(ballot & lt_mask), index);
+                }
+            }
+        }
+        {
+            const long long g0 = kProf ? clock64() : 0;
+            grid.sync();
+            if (kProf) pc[6] += clock64() - g0;
+        }
+        if (locked) break;
         step += n_step;
         iter++;
-        cur ^= 1;
+        max_rounds = 0;
     }
 
     // ---- epilogue: background + depth normalisation (renderer.py:375-376); all accumulators are final after the last barrier
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
-        const float ws = __ldcg(ra.weights_sum + n);
-        const float k = __fmul_rn(__fsub_rn(1.0f, ws), ra.bg_color);
+        const float ws_n = __ldcg(ra.weights_sum + n);
+        const float k = __fmul_rn(__fsub_rn(1.0f, ws_n), ra.bg_color);
         float *im = ra.image + (size_t)n * 3;
         im[0] = __fadd_rn(__ldcg(im), k); im[1] = __fadd_rn(__ldcg(im + 1), k); im[2] = __fadd_rn(__ldcg(im + 2), k);
         const float near = ra.nears[n], far = ra.fars[n];
         const float dd = __fsub_rn(__ldcg(ra.depth + n), near);
         ra.depth[n] = __fdiv_rn(dd < 0.f ? 0.f : dd, __fsub_rn(far, near));   // 0/0 = NaN for misses, like the reference
     }
-    if (blockIdx.x == 0 && tid == 0 && ra.stats) {
-        ra.stats[0] = (long long)iter;
-        ra.stats[1] = (long long)ra.ctr->samples;
-        ra.stats[2] = (long long)ra.ctr->tiles;
-        ra.stats[3] = 0;
+    if (kProf && lane == 0) {
+        pc[7] = clock64() - k_start;
+        pc[0] = pc[7] - (pc[1] + pc[2] + pc[3] + pc[4] + pc[5] + pc[6]);   // refill, bookkeeping, prologue, epilogue
+        for (int k = 0; k < 8; k++) atomicAdd(reinterpret_cast<unsigned long long *>(ra.prof + k), (unsigned long long)pc[k]);
+    }
+    if (ra.stats) {
+        const uint32_t wemit = warp_sum(tot_emitted);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) max_rounds = max(max_rounds, __shfl_xor_sync(0xffffffffu, max_rounds, d));
+        if (lane == 0) {
+            atomicAdd(&ra.ctr->samples, (unsigned long long)wemit);
+            atomicAdd(&ra.ctr->tiles, (unsigned long long)passes);
+            atomicMax(&ra.ctr->max_rounds, max_rounds);
+        }
+        grid.sync();   // every warp's counters are in
+        if (blockIdx.x == 0 && tid == 0) {
+            ra.stats[0] = (long long)iter + (long long)__ldcg(&ra.ctr->max_rounds);   // phase-A iterations + longest phase-B ray
+            ra.stats[1] = (long long)__ldcg(&ra.ctr->samples);
+            ra.stats[2] = (long long)__ldcg(&ra.ctr->tiles);
+            ra.stats[3] = (long long)iter;   // iterations that ended in a grid-wide barrier
+        }
     }
 }
 
@@ -448,18 +560,19 @@ struct ngp_ctx {
     uint32_t capN = 0;
     float *nears = nullptr, *fars = nullptr, *rays_t = nullptr;
     int *alive[2] = {nullptr, nullptr};
-    unsigned long long *status = nullptr;
-    size_t status_count = 0;
     RenderCtr *ctr = nullptr;
     // staging for ngp_render_host
     uint32_t capHost = 0;
     float *d_o = nullptr, *d_d = nullptr, *d_img = nullptr, *d_depth = nullptr, *d_ws = nullptr;
+    long long *prof = nullptr;    // device [8], allocated by ngp_ctx_enable_profile
     int render_blocks = 0, fwd_blocks = 0;
+    int march_budget = 12;        // cell probes per lane per pass (NGP_MARCH_BUDGET)
+    uint32_t lock_schedule = 1;   // NGP_RENDER_NOLOCK=1 keeps every iteration grid-synchronous (debugging / A-B timing)
     size_t render_smem = 0, fwd_smem = 0;
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return fwd_smem_bytes(nc) + kTile * 5 * 4; }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + (size_t)kRenderWarps * sizeof(WarpSmem); }
 
 extern "C" {
 
@@ -472,6 +585,10 @@ int ngp_ctx_create(ngp_ctx **out) {
     NGP_CUDA(cudaGetDevice(&c->device));
     NGP_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device));
     NGP_CUDA(cudaMalloc(&c->ctr, sizeof(RenderCtr)));
+    const char *nolock = getenv("NGP_RENDER_NOLOCK");
+    c->lock_schedule = (nolock && nolock[0] == '1') ? 0u : 1u;
+    const char *mb = getenv("NGP_MARCH_BUDGET");
+    if (mb && atoi(mb) > 0) c->march_budget = atoi(mb);
     *out = c;
     return 0;
 }
@@ -479,7 +596,7 @@ int ngp_ctx_create(ngp_ctx **out) {
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
     cudaFree(c->wpack); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]);
-    cudaFree(c->status); cudaFree(c->ctr); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
+    cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
     delete c;
     return 0;
 }
@@ -530,15 +647,36 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
     c->fwd_smem = fwd_smem_bytes(nc);
     c->render_smem = render_smem_bytes(nc);
     NGP_CUDA(cudaFuncSetAttribute(k_network_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_smem));
-    NGP_CUDA(cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem));
+    NGP_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem));
+    NGP_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem));
     int occ = 0;
     NGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_network_forward, kTile, c->fwd_smem));
     NGP_REQUIRE(occ >= 1, "network_forward kernel does not fit on an SM (smem %zu B)", c->fwd_smem);
     c->fwd_blocks = occ * c->sm_count;
-    NGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render, kTile, c->render_smem));
+    NGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render<false>, kRenderThreads, c->render_smem));
     NGP_REQUIRE(occ >= 1, "render kernel does not fit on an SM (smem %zu B)", c->render_smem);
     c->render_blocks = occ * c->sm_count;
     c->has_net = true;
+    return 0;
+}
+
+int ngp_ctx_enable_profile(ngp_ctx *c, int enable) {
+    NGP_REQUIRE(c != nullptr, "ctx_enable_profile: null ctx");
+    if (enable && !c->prof) {
+        NGP_CUDA(cudaMalloc(&c->prof, 8 * sizeof(long long)));
+        NGP_CUDA(cudaMemset(c->prof, 0, 8 * sizeof(long long)));
+    } else if (!enable && c->prof) {
+        cudaFree(c->prof);
+        c->prof = nullptr;
+    }
+    return 0;
+}
+
+int ngp_ctx_phase_cycles(ngp_ctx *c, int64_t *out_host, int reset) {
+    NGP_REQUIRE(c != nullptr && c->prof != nullptr && out_host != nullptr, "ctx_phase_cycles: profiling is not enabled (ngp_ctx_enable_profile)");
+    NGP_CUDA(cudaDeviceSynchronize());
+    NGP_CUDA(cudaMemcpy(out_host, c->prof, 8 * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (reset) NGP_CUDA(cudaMemset(c->prof, 0, 8 * sizeof(long long)));
     return 0;
 }
 
@@ -568,7 +706,7 @@ int ngp_network_forward(ngp_ctx *c, const float *xyzs, const float *dirs, uint32
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     if (N <= c->capN) return 0;
-    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->status);
+    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]);
     c->capN = 0;
     const uint32_t cap = N + N / 8 + 1024;
     NGP_CUDA(cudaMalloc(&c->nears, sizeof(float) * cap));
@@ -576,8 +714,6 @@ static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     NGP_CUDA(cudaMalloc(&c->rays_t, sizeof(float) * cap));
     NGP_CUDA(cudaMalloc(&c->alive[0], sizeof(int) * cap));
     NGP_CUDA(cudaMalloc(&c->alive[1], sizeof(int) * cap));
-    c->status_count = cap / 16 + 64;   // >= max tiles of any iteration (n_step = k => <= N/k rays, floor(128/k) rays per tile)
-    NGP_CUDA(cudaMalloc(&c->status, sizeof(unsigned long long) * c->status_count));
     c->capN = cap;
     return 0;
 }
@@ -591,17 +727,16 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     if (int rc = ensure_workspace(c, N)) return rc;
     cudaStream_t st = as_stream(stream);
     NGP_CUDA(cudaMemsetAsync(c->ctr, 0, sizeof(RenderCtr), st));
-    NGP_CUDA(cudaMemsetAsync(c->status, 0, sizeof(unsigned long long) * c->status_count, st));
     RenderArgs ra{};
-    ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps;
+    ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps; ra.lock_schedule = c->lock_schedule; ra.march_budget = c->march_budget;
     for (int i = 0; i < 6; i++) ra.aabb[i] = c->aabb[i];
     ra.mc = make_march_const(c->nc.bound, dt_gamma, max_steps, c->cascade, c->grid_size, c->bitfield);
     ra.nears = c->nears; ra.fars = c->fars; ra.rays_t = c->rays_t; ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1];
-    ra.status = c->status; ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
-    ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats);
+    ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
+    ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     NetConst nc = c->nc;
     void *args[] = {&nc, &ra};
-    NGP_CUDA(cudaLaunchCooperativeKernel((const void *)k_render, dim3(c->render_blocks), dim3(kTile), args, c->render_smem, st));
+    NGP_CUDA(cudaLaunchCooperativeKernel(c->prof ? (const void *)k_render<true> : (const void *)k_render<false>, dim3(c->render_blocks), dim3(kRenderThreads), args, c->render_smem, st));
     return after_launch("render");
 }
 

@@ -34,6 +34,7 @@ def sass_lines(path, kernel):
 def main():
     src_csv, sass, kernel = sys.argv[1:4]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+    sort_key = sys.argv[5] if len(sys.argv) > 5 else "samples"   # or "inst"
     rows = list(csv.reader(open(src_csv)))
     hdr_i = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[hdr_i]
@@ -50,12 +51,14 @@ def main():
         total += n
         agg[key]["samples"] += n
         agg[key]["inst"] += float(r[col["Instructions Executed"]] or 0)
+        agg[key]["tinst"] += float(r[col["Thread Instructions Executed"]] or 0)
         for s in stalls:
             agg[key][s] += float(r[col[s]] or 0)
-    print(f"total samples {total:.0f}")
-    for key, a in sorted(agg.items(), key=lambda kv: -kv[1]["samples"])[:top]:
+    ti = sum(a["inst"] for a in agg.values())
+    print(f"total samples {total:.0f}, warp instructions {ti:.4g}, thread instructions {sum(a['tinst'] for a in agg.values()):.4g}")
+    for key, a in sorted(agg.items(), key=lambda kv: -kv[1][sort_key])[:top]:
         tops = sorted(((a[s], s[6:]) for s in stalls), reverse=True)[:3]
-        print(f"{key[0]}:{key[1]:<5d} {100 * a['samples'] / total:5.1f}%  inst {a['inst']:.3g}  " + "  ".join(f"{n}={100 * v / max(a['samples'], 1):.0f}%" for v, n in tops))
+        print(f"{key[0]}:{key[1]:<5d} {100 * a['samples'] / total:5.1f}%  inst {a['inst']:.3g} ({100 * a['inst'] / ti:.1f}%, {a['tinst'] / max(a['inst'], 1):.0f} thr)  " + "  ".join(f"{n}={100 * v / max(a['samples'], 1):.0f}%" for v, n in tops))
 
 
 if __name__ == "__main__":

@@ -139,8 +139,10 @@ __device__ __forceinline__ RayDir make_ray_dir(float dx, float dy, float dz) {
 // the ray at t.  Occupied: returns true with the sample (x, y, z, dt, delta_t = t_new - last_t) and t advanced by dt.
 // Empty: returns false with t advanced, in dt increments, past the cell's exit.  The loop state is just (t, last_t), so a
 // caller may interleave the probes of 32 rays in lockstep (the persistent renderer) or run them to completion (march_ray).
+// `coarse` (optional, shared memory): one bit per aligned 4x4x4 block of cells = 64 consecutive Morton indices, set iff any of
+// them is occupied.  A clear bit answers the probe without the dependent global load; the result is the reference's either way.
 __device__ __forceinline__ bool march_probe(const MarchConst &m, float ox, float oy, float oz, const RayDir &rd, float &t, float &last_t,
-                                            float &x, float &y, float &z, float &dt, float &delta_t) {
+                                            float &x, float &y, float &z, float &dt, float &delta_t, const uint32_t *coarse = nullptr) {
     const bool one_level = m.cm1f == 0.0f;     // cascade 1 (bound <= 1): the mip level is always 0
     const bool const_dt = m.dt_gamma == 0.0f;  // dt = clamp(t * 0, dt_min, dt_max) for every t (NaN-safe: fmaxf drops the NaN)
     const float dt0 = fminf(m.dt_max, fmaxf(m.dt_min, 0.0f));
@@ -160,7 +162,9 @@ __device__ __forceinline__ bool march_probe(const MarchConst &m, float ox, float
     const int ny = cell_coord(y, mip_rbound, m);
     const int nz = cell_coord(z, mip_rbound, m);
     const uint32_t idx = (uint32_t)__fmaf_rn(m.H3f, (float)level, (float)morton3d(nx, ny, nz));
-    const bool occ = (__ldg(m.grid + (idx >> 3)) >> (idx & 7)) & 1;
+    bool occ = true;
+    if (coarse) occ = (coarse[idx >> 11] >> ((idx >> 6) & 31u)) & 1u;
+    if (occ) occ = (__ldg(m.grid + (idx >> 3)) >> (idx & 7)) & 1;
     if (occ) {
         t = __fadd_rn(t, dt);
         delta_t = __fsub_rn(t, last_t);

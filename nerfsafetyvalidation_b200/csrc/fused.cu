@@ -11,6 +11,7 @@
 #include <cooperative_groups.h>
 #include <float.h>
 #include <stddef.h>
+#include <stdint.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -35,11 +36,11 @@ struct NetConst {
 };
 
 struct RenderCtr {
-    uint32_t n_alive[3];
-    uint32_t ticket[3];
-    uint32_t cursor, max_rounds;
+    uint32_t n_alive[3];    // live rays of iteration k at [k % 3]
+    uint32_t cursor[3];     // MARCH phase: next unclaimed entry of the live list
+    uint32_t ticket[3];     // EVALUATE phase: next unclaimed 32-ray tile
+    uint32_t pad;
     unsigned long long samples;
-    unsigned long long tiles;
 };
 
 // ---------------------------------------------------------------------------------------------- device pieces
@@ -186,6 +187,15 @@ __device__ __forceinline__ void mlp_rows32(const NetConst &nc, const uint2 *__re
     }
 }
 
+// ---------------------------------------------------------------------------------------------- coarse occupancy
+// bit j of the result <- any of the 64 cells with Morton index 64 j .. 64 j + 63 (an aligned 4x4x4 block) is occupied.
+__global__ void k_coarse_occupancy(const unsigned long long *__restrict__ bitfield64, uint32_t n_blocks, uint32_t *__restrict__ coarse) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool any = j < n_blocks && __ldg(bitfield64 + j) != 0ull;
+    const uint32_t word = __ballot_sync(0xffffffffu, any);
+    if ((threadIdx.x & 31) == 0 && j < n_blocks) coarse[j >> 5] = word;
+}
+
 // ---------------------------------------------------------------------------------------------- weight packing
 // sigma: [64][32], nh x [64][64], [16][64]; colour: [64][32]*, nh x [64][64], [16][64]   (* input columns shifted:
 // packed column 16 <- zero, packed columns 17..31 <- source columns 16..30; source column 31 multiplies the zero pad).
@@ -238,35 +248,31 @@ k_network_forward(NetConst nc, const float *__restrict__ xyzs, const float *__re
 }
 
 // ---------------------------------------------------------------------------------------------- persistent renderer
-// Warp-autonomous design: one CTA of 16 warps per SM and NO block-level barrier after the prologue.  Lane r of a warp owns
-// ray r of the warp's current group and that ray's accumulators.  One "chunk" (= one reference loop iteration for those rays):
-//   march     every lane marches its ray for up to n_step samples (registers -> per-warp smem records, raymarching.cu:706-814)
-//   evaluate  the warp's samples, densely packed ray-major (so consecutive rows are consecutive samples of one ray and share
-//             hash-grid cells), go through {16-level gather -> sigma MLP -> SH + colour MLP} 32 rows at a time on tensor cores
-//   composite every lane accumulates its own samples front to back in registers with early termination (:828-913)
-// so xyz / dirs / deltas / sigmas / rgbs never exist in global memory.  Latency is hidden by the other 15 warps of the SM being
-// in other phases of their own chunks.
+// NeRFRenderer.run_cuda's inference loop (nerf/renderer.py:329-376) as ONE persistent cooperative launch, one 16-warp CTA per
+// SM.  The reference's global schedule `n_step = clamp(N // n_alive, 1, 8)` (renderer.py:357) is kept exactly -- per-ray sample
+// counts and the rays_t recurrence depend on it -- so the grid meets twice per iteration:
 //
-// Schedule.  `n_step = clamp(N // n_alive, 1, 8)` (renderer.py:357) is global, and the per-ray chunking is visible in the
-// results (rays_t restarts from the compositor's sum of deltas at every chunk boundary), so:
-//   phase A  while n_step < 8: one grid-wide barrier per iteration; warps pull 32-ray groups from an atomic ticket and append
-//            survivors to the next live list with one ballot + one atomicAdd per warp (list order is not the reference's,
-//            which no per-ray output depends on; the stand-alone compact_alive op keeps the stable order);
-//   phase B  once n_alive <= N / 8 the schedule is locked at 8 for good (n_alive never grows), so every ray's remaining
-//            chunking is known: warps keep their rays in registers chunk after chunk, refill dead lanes from the live list,
-//            and the grid does not meet again until the epilogue.  Per-ray results are identical to the iteration-synchronous
-//            loop; iterations = phase-A iterations + the longest phase-B ray.
+//   MARCH     lane-level dynamic scheduling: every LANE owns one live ray, probes the occupancy bitfield one cell per trip in
+//             lockstep with the other 31 lanes of its warp (so the warp stays converged whatever mix of occupied / empty cells
+//             its rays cross), and the moment its ray has its n_step samples (or leaves the box) the lane takes the next live
+//             ray from the list (warp ballot + prefix, one atomic per warp per refill).  Samples go to an L2-resident buffer in
+//             the reference's row order (row = n * n_step + s, raymarching.cu:732-734): 20 B per sample, no dirs.
+//   EVALUATE  warp w pulls tiles of 32 live rays = 32 * n_step consecutive sample rows (consecutive rows are consecutive samples
+//   + COMPOSITE  of one ray and share hash-grid cells): 16-level gather -> sigma MLP -> SH + colour MLP, 32 rows at a time on
+//             tensor cores with the weights resident in shared memory; then lane r composites ray r front to back in registers
+//             with early termination (raymarching.cu:828-913) and the survivors are appended to the next live list with one
+//             ballot + one atomicAdd per warp (list order is not the reference's, which no per-ray output depends on; the
+//             stand-alone compact_alive op keeps the stable order).
+// xyz / deltas make one trip through L2; dirs / sigmas / rgbs never exist in memory.
 constexpr int kRenderThreads = 512;
 constexpr int kRenderWarps = kRenderThreads / 32;
 constexpr int kMaxStep = 8;                    // renderer.py:357
-constexpr int kSlotStride = kMaxStep + 1;      // lane-major sample slots, odd stride => conflict-free for lane- and row-order access
-constexpr int kSlots = 32 * kSlotStride;
+constexpr int kTileRows = 32 * kMaxStep;       // sample rows of one 32-ray tile
+constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
 
 struct WarpSmem {
-    float x[kSlots], y[kSlots], z[kSlots];     // sample position; after the MLPs: sigma, half2(r, g) bits, b
-    float dt[kSlots], dl[kSlots];              // deltas[:, 0], deltas[:, 1]
-    float ray[6 * 32];                         // [k][lane]: origin and direction of the lane's ray
-    uint16_t rowmap[32 * kMaxStep];            // dense sample row -> (lane << 4) | s
+    float sigma[kTileRows], rg[kTileRows], b[kTileRows];   // network outputs per row (rg = half2 bits: rgb are half-rounded)
+    float dt[kTileRows], dl[kTileRows];                    // deltas[:, 0], deltas[:, 1]
     __half enc[32 * kEncStride];               // A-operand staging of the current 32 rows; first 16 B of a row = (sigma, r, g, b) after the MLPs
     __half sh[32 * kShStride];                 // degree-4 SH of lane r's ray direction
 };
@@ -276,12 +282,15 @@ struct RenderArgs {
     const float *rays_o, *rays_d;
     uint32_t N;
     float min_near, bg_color;
-    uint32_t max_steps, lock_schedule;
-    int march_budget;
+    uint32_t max_steps;
     float aabb[6];
     MarchConst mc;
     float *nears, *fars, *rays_t;
     int *alive[2];
+    const uint32_t *coarse;   // [coarse_words] 4x4x4-block occupancy bits (Morton order) or NULL
+    uint32_t coarse_words;
+    float4 *smp_a;     // [N] (x, y, z, dt) per sample row of the current iteration
+    float *smp_b;      // [N] t_new - last_t
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -289,104 +298,158 @@ struct RenderArgs {
     long long *prof;   // optional [8]: warp-cycles per phase (diagnostics, ngp_ctx_phase_cycles)
 };
 
-// One PASS of a warp over its 32 ray slots.  Every marching lane advances its ray by at most `march_budget` cell probes
-// towards the n_step samples of its current chunk (time-slicing: a lane crossing a long empty stretch spends several passes
-// on it while its neighbours keep producing samples); the samples produced in this pass are evaluated, densely packed
-// ray-major, 32 rows at a time, and composited by their own lanes.  Chunk semantics (raymarching.cu:706-814, 828-913) are kept
-// by the caller: `emitted` counts the chunk's samples so far, `exhausted` = the marcher reached `far`, `terminated` = T < 1e-4.
-template <bool kProf>
-__device__ __forceinline__ void warp_pass(const NetConst &nc, const RenderArgs &ra, const uint2 *__restrict__ s_w, WarpSmem &ws, int lane,
-                                          bool marching, uint32_t n_step, float &tm, float &last_t, float far, RayAcc &a, uint32_t &emitted,
-                                          bool &terminated, bool &exhausted, long long (&pc)[8]) {
-    uint32_t produced = 0;
-    long long c0 = kProf ? clock64() : 0, c1;
-#define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
-    {
-        const float ox = ws.ray[lane], oy = ws.ray[32 + lane], oz = ws.ray[64 + lane];
-        const RayDir rd = make_ray_dir(ws.ray[96 + lane], ws.ray[128 + lane], ws.ray[160 + lane]);
-        float x, y, z, dt, dl;
-        // lockstep: every lane probes one cell per trip, so the warp stays converged whatever mix of occupied / empty
-        // cells its 32 rays are crossing (a per-lane `while` would leave the few lanes in empty space running alone)
-        for (int p = 0; p < ra.march_budget; p++) {
-            const bool go = marching && emitted < n_step && tm < far;
-            if (!__any_sync(0xffffffffu, go)) break;
-            if (go && march_probe(ra.mc, ox, oy, oz, rd, tm, last_t, x, y, z, dt, dl)) {
-                if (!terminated) {   // after T-termination the rest of the chunk is only counted (samples_per_ray parity)
-                    const int slot = lane * kSlotStride + (int)produced;
-                    ws.x[slot] = x; ws.y[slot] = y; ws.z[slot] = z; ws.dt[slot] = dt; ws.dl[slot] = dl;
-                    produced++;
+// MARCH phase of one iteration for one warp (see the header comment).  Returns the samples this lane emitted.
+__device__ __forceinline__ uint32_t march_phase(const RenderArgs &ra, const uint32_t *s_coarse, int lane, uint32_t lt_mask,
+                                                const int *__restrict__ alive_in, uint32_t n_alive, uint32_t n_step, uint32_t *cursor) {
+    bool has = false, list_done = false;
+    uint32_t n = 0, emitted = 0, total = 0;
+    int index = 0;
+    float ox = 0.f, oy = 0.f, oz = 0.f, tm = 0.f, last_t = 0.f, far = 0.f;
+    RayDir rd = make_ray_dir(1.f, 1.f, 1.f);
+    for (;;) {
+        const uint32_t need = __ballot_sync(0xffffffffu, !has);
+        if (!list_done && __popc(need) >= kRefillLanes) {
+            const uint32_t cnt = (uint32_t)__popc(need);
+            uint32_t start = 0;
+            if (lane == 0) start = atomicAdd(cursor, cnt);
+            start = __shfl_sync(0xffffffffu, start, 0);
+            if (!has) {
+                const uint32_t my = start + (uint32_t)__popc(need & lt_mask);
+                if (my < n_alive) {
+                    n = my;
+                    index = __ldcg(alive_in + n);
+                    const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
+                    ox = __ldg(o); oy = __ldg(o + 1); oz = __ldg(o + 2);
+                    rd = make_ray_dir(__ldg(d), __ldg(d + 1), __ldg(d + 2));
+                    tm = __ldcg(ra.rays_t + index);
+                    last_t = tm;
+                    far = __ldcg(ra.fars + index);
+                    emitted = 0;
+                    has = true;
                 }
+            }
+            list_done = start + cnt >= n_alive;
+        }
+        if (!__any_sync(0xffffffffu, has)) {
+            if (list_done) break;
+            continue;
+        }
+        if (has) {   // one lockstep probe
+            float x, y, z, dt, dl;
+            if (tm < far && march_probe(ra.mc, ox, oy, oz, rd, tm, last_t, x, y, z, dt, dl, s_coarse)) {
+                const size_t row = (size_t)n * n_step + emitted;
+                __stcg(ra.smp_a + row, make_float4(x, y, z, dt));
+                __stcg(ra.smp_b + row, dl);
                 emitted++;
             }
-        }
-        if (marching) exhausted = emitted < n_step && !(tm < far);
-    }
-    NGP_PROF(1)
-    const uint32_t incl = warp_inclusive_sum(produced, lane);
-    const uint32_t base = incl - produced, total = __shfl_sync(0xffffffffu, incl, 31);
-    if (total == 0) return;
-    for (uint32_t s = 0; s < produced; s++) ws.rowmap[base + s] = (uint16_t)((lane << 4) | s);
-    __syncwarp();
-    NGP_PROF(2)
-    for (uint32_t row0 = 0; row0 < total; row0 += 32) {
-        const uint32_t row = row0 + lane;
-        const bool valid = row < total;
-        int slot = 0;
-        if (valid) {
-            const uint32_t m = ws.rowmap[row];
-            slot = (int)(m >> 4) * kSlotStride + (int)(m & 15u);
-            encode_point(nc, ws.x[slot], ws.y[slot], ws.z[slot], reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
+            if (emitted == n_step || !(tm < far)) {      // chunk complete (raymarching.cu:752) or ray exhausted
+                for (uint32_t s = emitted; s < n_step; s++) {   // un-emitted rows read as delta == 0 (raymarching.py:329-331)
+                    const size_t row = (size_t)n * n_step + s;
+                    __stcg(ra.smp_a + row, make_float4(0.f, 0.f, 0.f, 0.f));
+                    __stcg(ra.smp_b + row, 0.f);
+                }
+                if (ra.samples_per_ray && emitted) ra.samples_per_ray[index] += (int)emitted;
+                total += emitted;
+                has = false;
+            }
         }
         __syncwarp();
-        NGP_PROF(3)
-        mlp_rows32(nc, s_w, ws.enc,
-                   [&](int r) {
-                       const uint32_t rr = row0 + (uint32_t)r;
-                       const uint32_t ln = rr < total ? (uint32_t)(ws.rowmap[rr] >> 4) : 0u;
-                       return ws.sh + ln * kShStride;
-                   },
-                   0, lane, [&](int r, float sg) { reinterpret_cast<float *>(ws.enc + r * kEncStride)[0] = sg; },
-                   [&](int r, int t, float c0, float c1) {
-                       float *o = reinterpret_cast<float *>(ws.enc + r * kEncStride);
-                       if (t == 0) { o[1] = c0; o[2] = c1; } else { o[3] = c0; }
-                   });
-        __syncwarp();
-        NGP_PROF(4)
-        if (valid) {
-            const float4 o = *reinterpret_cast<const float4 *>(ws.enc + lane * kEncStride);
-            ws.x[slot] = o.x; ws.y[slot] = __uint_as_float(pack_half2(o.y, o.z)); ws.z[slot] = o.w;   // rgb are half-rounded: exact
+    }
+    return total;
+}
+
+// EVALUATE + COMPOSITE phase of one iteration for one warp (see the header comment).
+template <bool kProf>
+__device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs &ra, const uint2 *__restrict__ s_w, WarpSmem &ws, int lane,
+                                           uint32_t lt_mask, const int *__restrict__ alive_in, int *__restrict__ alive_out, uint32_t n_alive,
+                                           uint32_t n_step, uint32_t *ticket, uint32_t *next_count, long long (&pc)[8]) {
+    const uint32_t n_tiles = (n_alive + 31) / 32;
+    long long c0 = kProf ? clock64() : 0, c1;
+#define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
+    uint32_t next_tile = 0;
+    if (lane == 0) next_tile = atomicAdd(ticket, 1u);
+    for (;;) {
+        const uint32_t tile = __shfl_sync(0xffffffffu, next_tile, 0);
+        if (tile >= n_tiles) break;
+        if (lane == 0) next_tile = atomicAdd(ticket, 1u);   // claimed now, needed a whole tile later: its latency is hidden
+        const uint32_t n = tile * 32 + lane;
+        const bool has_ray = n < n_alive;
+        int index = 0;
+        RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (has_ray) {
+            index = __ldcg(alive_in + n);
+            const float *d = ra.rays_d + (size_t)index * 3;
+            uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + lane * kShStride);
+            sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), srow[0], srow[1]);   // the direction is constant along the ray
+            a.t = __ldcg(ra.rays_t + index); a.ws = __ldcg(ra.weights_sum + index); a.d = __ldcg(ra.depth + index);
+            a.r = __ldcg(ra.image + (size_t)index * 3); a.g = __ldcg(ra.image + (size_t)index * 3 + 1); a.b = __ldcg(ra.image + (size_t)index * 3 + 2);
         }
+        const uint32_t tile_rays = min(32u, n_alive - tile * 32);
+        const uint32_t rows = tile_rays * n_step;
+        const size_t row_base = (size_t)tile * 32 * n_step;
+        NGP_PROF(0)
+        for (uint32_t row0 = 0; row0 < rows; row0 += 32) {
+            const uint32_t r = row0 + lane;
+            float4 sa = make_float4(0.f, 0.f, 0.f, 0.f);
+            float sb = 0.f;
+            if (r < rows) {
+                sa = __ldcg(ra.smp_a + row_base + r);
+                sb = __ldcg(ra.smp_b + row_base + r);
+            }
+            ws.dt[r] = sa.w; ws.dl[r] = sb;
+            const bool live = sa.w != 0.f;                       // delta == 0 is the reference's end-of-ray sentinel
+            if (live) encode_point(nc, sa.x, sa.y, sa.z, reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
+            __syncwarp();
+            NGP_PROF(3)
+            if (__any_sync(0xffffffffu, live)) {
+                mlp_rows32(nc, s_w, ws.enc,
+                           [&](int rr) {
+                               const uint32_t ray = min((row0 + (uint32_t)rr) / n_step, 31u);
+                               return ws.sh + ray * kShStride;
+                           },
+                           0, lane, [&](int rr, float sg) { reinterpret_cast<float *>(ws.enc + rr * kEncStride)[0] = sg; },
+                           [&](int rr, int t, float v0, float v1) {
+                               float *o = reinterpret_cast<float *>(ws.enc + rr * kEncStride);
+                               if (t == 0) { o[1] = v0; o[2] = v1; } else { o[3] = v0; }
+                           });
+                __syncwarp();
+                if (live) {
+                    const float4 o = *reinterpret_cast<const float4 *>(ws.enc + lane * kEncStride);
+                    ws.sigma[r] = o.x; ws.rg[r] = __uint_as_float(pack_half2(o.y, o.z)); ws.b[r] = o.w;   // rgb are half-rounded: exact
+                }
+            }
+            __syncwarp();
+            NGP_PROF(4)
+        }
+        // ---- composite (raymarching.cu:828-913): lane r <-> ray r, rows r * n_step .. + n_step - 1
+        bool survives = false;
+        if (has_ray) {
+            uint32_t s = 0;
+            while (s < n_step) {
+                const uint32_t r = lane * n_step + s;
+                const float dt = ws.dt[r];
+                if (dt == 0.f) break;
+                const uint32_t rg = __float_as_uint(ws.rg[r]);
+                const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&rg));
+                if (composite_sample(a, ws.sigma[r], c.x, c.y, ws.b[r], dt, ws.dl[r])) break;
+                s++;
+            }
+            survives = s == n_step;
+            if (survives) __stcg(ra.rays_t + index, a.t);                       // raymarching.cu:905-911
+            __stcg(ra.weights_sum + index, a.ws); __stcg(ra.depth + index, a.d);
+            __stcg(ra.image + (size_t)index * 3, a.r); __stcg(ra.image + (size_t)index * 3 + 1, a.g); __stcg(ra.image + (size_t)index * 3 + 2, a.b);
+        }
+        const uint32_t ballot = __ballot_sync(0xffffffffu, survives);   // renderer.py:369
+        if (ballot) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(next_count, (uint32_t)__popc(ballot));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (survives) __stcg(alive_out + base + __popc(ballot & lt_mask), index);
+        }
+        __syncwarp();   // ws is rewritten by the next tile
+        NGP_PROF(5)
     }
-    __syncwarp();
-    for (uint32_t s = 0; s < produced; s++) {
-        const int slot = lane * kSlotStride + (int)s;
-        const uint32_t rg = __float_as_uint(ws.y[slot]);
-        const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&rg));
-        if (composite_sample(a, ws.x[slot], c.x, c.y, ws.z[slot], ws.dt[slot], ws.dl[slot])) { terminated = true; break; }
-    }
-    __syncwarp();   // the records are rewritten by the next pass
-    NGP_PROF(5)
 #undef NGP_PROF
-}
-
-__device__ __forceinline__ void load_ray(const RenderArgs &ra, WarpSmem &ws, int lane, int index, float &tm, float &last_t, float &far, RayAcc &a) {
-    const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
-    const float dx = __ldg(d), dy = __ldg(d + 1), dz = __ldg(d + 2);
-    ws.ray[lane] = __ldg(o); ws.ray[32 + lane] = __ldg(o + 1); ws.ray[64 + lane] = __ldg(o + 2);
-    ws.ray[96 + lane] = dx; ws.ray[128 + lane] = dy; ws.ray[160 + lane] = dz;
-    uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + lane * kShStride);
-    sh_to_half(dx, dy, dz, srow[0], srow[1]);   // the direction is constant along the ray
-    tm = __ldcg(ra.rays_t + index);
-    last_t = tm;
-    far = __ldcg(ra.fars + index);
-    a.t = tm; a.ws = __ldcg(ra.weights_sum + index); a.d = __ldcg(ra.depth + index);
-    a.r = __ldcg(ra.image + (size_t)index * 3); a.g = __ldcg(ra.image + (size_t)index * 3 + 1); a.b = __ldcg(ra.image + (size_t)index * 3 + 2);
-}
-
-__device__ __forceinline__ void store_ray(const RenderArgs &ra, int index, const RayAcc &a, bool survives) {
-    if (survives) __stcg(ra.rays_t + index, a.t);                       // raymarching.cu:905-911
-    __stcg(ra.weights_sum + index, a.ws); __stcg(ra.depth + index, a.d);
-    __stcg(ra.image + (size_t)index * 3, a.r); __stcg(ra.image + (size_t)index * 3 + 1, a.g); __stcg(ra.image + (size_t)index * 3 + 2, a.b);
 }
 
 template <bool kProf>
@@ -396,10 +459,14 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     uint2 *s_w = reinterpret_cast<uint2 *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpSmem &ws = reinterpret_cast<WarpSmem *>(s_w + nc.wpack_count)[warp];
+    uint32_t *s_coarse = ra.coarse ? reinterpret_cast<uint32_t *>(reinterpret_cast<WarpSmem *>(s_w + nc.wpack_count) + kRenderWarps) : nullptr;
     const uint32_t N = ra.N;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const bool counting = ra.samples_per_ray != nullptr || ra.stats != nullptr;
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long k_start = kProf ? clock64() : 0;
     copy_wpack_to_smem(nc, s_w);
+    if (s_coarse)
+        for (uint32_t i = tid; i < ra.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(ra.coarse + i);
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
@@ -416,95 +483,31 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     if (blockIdx.x == 0 && tid == 0) ra.ctr->n_alive[0] = N;   // all counters were zeroed by the host before the launch
     grid.sync();
 
-    uint32_t step = 0, iter = 0, tot_emitted = 0, passes = 0, max_rounds = 0;
-    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    const long long k_start = kProf ? clock64() : 0;
-    // One trip of this loop = one reference iteration (phase A, grid barrier at its end) or, once the schedule is locked at
-    // n_step = 8, the whole rest of the frame (phase B, rays stay in their lanes chunk after chunk).
+    uint32_t step = 0, iter = 0, tot_emitted = 0;
     while (step < ra.max_steps) {
         const uint32_t n_alive = __ldcg(&ra.ctr->n_alive[iter % 3]);
         if (n_alive == 0) break;
         uint32_t n_step = N / n_alive;                                  // renderer.py:357
         n_step = n_step > kMaxStep ? kMaxStep : (n_step < 1 ? 1 : n_step);
-        const bool locked = n_step == kMaxStep && ra.lock_schedule;     // n_alive never grows => n_step stays 8 for good
         const int *alive_in = ra.alive[iter & 1];
         int *alive_out = ra.alive[(iter & 1) ^ 1];
-        uint32_t *cursor = &ra.ctr->ticket[iter % 3];
-        uint32_t *next_count = &ra.ctr->n_alive[(iter + 1) % 3];
-        if (blockIdx.x == 0 && tid == 0) {   // neither word is touched by anyone else during this iteration
-            ra.ctr->ticket[(iter + 1) % 3] = 0;
+        const uint32_t slot = iter % 3, nslot = (iter + 1) % 3;
+        if (blockIdx.x == 0 && tid == 0) {   // none of these words is touched by anyone else during this iteration
+            ra.ctr->cursor[nslot] = 0;
+            ra.ctr->ticket[nslot] = 0;
             ra.ctr->n_alive[(iter + 2) % 3] = 0;
         }
-
-        bool has_ray = false, list_done = false, terminated = false, exhausted = false;
-        int index = 0, spr = 0;
-        float tm = 0.f, last_t = 0.f, far = 0.f;
-        RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        uint32_t emitted = 0, ray_step = 0, rounds = 0;
-        for (;;) {
-            // ---- refill free lanes from the live list (one atomic per warp)
-            const uint32_t need = __ballot_sync(0xffffffffu, !has_ray);
-            if (need && !list_done) {
-                const uint32_t cnt = (uint32_t)__popc(need);
-                uint32_t start = 0;
-                if (lane == 0) start = atomicAdd(cursor, cnt);
-                start = __shfl_sync(0xffffffffu, start, 0);
-                if (!has_ray) {
-                    const uint32_t my = start + (uint32_t)__popc(need & lt_mask);
-                    if (my < n_alive) {
-                        index = __ldcg(alive_in + my);
-                        load_ray(ra, ws, lane, index, tm, last_t, far, a);
-                        has_ray = true; terminated = false; exhausted = false;
-                        emitted = 0; ray_step = step; rounds = 1; spr = 0;
-                    }
-                }
-                list_done = start + cnt >= n_alive;
-            }
-            if (!__any_sync(0xffffffffu, has_ray)) break;
-
-            warp_pass<kProf>(nc, ra, s_w, ws, lane, has_ray, n_step, tm, last_t, far, a, emitted, terminated, exhausted, pc);
-            passes++;
-
-            // ---- chunk bookkeeping (renderer.py:347-373)
-            const bool chunk_done = has_ray && (exhausted || emitted == n_step || (terminated && !counting));
-            bool survives = chunk_done && !terminated && !exhausted;
-            bool retire = chunk_done;
-            if (chunk_done) {
-                tot_emitted += emitted;
-                spr += (int)emitted;
-                if (locked && survives && ray_step + kMaxStep < ra.max_steps) {
-                    // next reference iteration for this ray, without leaving the lane: the marcher restarts from the
-                    // compositor's t (rays_t, raymarching.cu:905) exactly as the reference's next march_rays call does
-                    ray_step += kMaxStep; rounds++;
-                    tm = a.t; last_t = tm; emitted = 0;
-                    retire = false;
-                }
-            }
-            if (retire) {
-                store_ray(ra, index, a, survives);
-                if (ra.samples_per_ray && spr) ra.samples_per_ray[index] += spr;
-                max_rounds = max(max_rounds, rounds);
-                has_ray = false;
-            }
-            if (!locked) {                                               // renderer.py:369
-                const uint32_t ballot = __ballot_sync(0xffffffffu, retire && survives);
-                if (ballot) {
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(next_count, (uint32_t)__popc(ballot));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (retire && survives) __stcg(alive_out + base + __popc(ballot & lt_mask), index);
-                }
-            }
-        }
-        {
-            const long long g0 = kProf ? clock64() : 0;
-            grid.sync();
-            if (kProf) pc[6] += clock64() - g0;
-        }
-        if (locked) break;
+        long long g0 = kProf ? clock64() : 0;
+        tot_emitted += march_phase(ra, s_coarse, lane, lt_mask, alive_in, n_alive, n_step, &ra.ctr->cursor[slot]);
+        if (kProf) { const long long g1 = clock64(); pc[1] += g1 - g0; g0 = g1; }
+        grid.sync();
+        if (kProf) pc[2] += clock64() - g0;
+        eval_phase<kProf>(nc, ra, s_w, ws, lane, lt_mask, alive_in, alive_out, n_alive, n_step, &ra.ctr->ticket[slot], &ra.ctr->n_alive[nslot], pc);
+        if (kProf) g0 = clock64();
+        grid.sync();
+        if (kProf) pc[6] += clock64() - g0;
         step += n_step;
         iter++;
-        max_rounds = 0;
     }
 
     // ---- epilogue: background + depth normalisation (renderer.py:375-376); all accumulators are final after the last barrier
@@ -519,24 +522,18 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     }
     if (kProf && lane == 0) {
         pc[7] = clock64() - k_start;
-        pc[0] = pc[7] - (pc[1] + pc[2] + pc[3] + pc[4] + pc[5] + pc[6]);   // refill, bookkeeping, prologue, epilogue
+        pc[0] += pc[7] - (pc[0] + pc[1] + pc[2] + pc[3] + pc[4] + pc[5] + pc[6]);   // + prologue, epilogue, loop control
         for (int k = 0; k < 8; k++) atomicAdd(reinterpret_cast<unsigned long long *>(ra.prof + k), (unsigned long long)pc[k]);
     }
     if (ra.stats) {
         const uint32_t wemit = warp_sum(tot_emitted);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) max_rounds = max(max_rounds, __shfl_xor_sync(0xffffffffu, max_rounds, d));
-        if (lane == 0) {
-            atomicAdd(&ra.ctr->samples, (unsigned long long)wemit);
-            atomicAdd(&ra.ctr->tiles, (unsigned long long)passes);
-            atomicMax(&ra.ctr->max_rounds, max_rounds);
-        }
+        if (lane == 0) atomicAdd(&ra.ctr->samples, (unsigned long long)wemit);
         grid.sync();   // every warp's counters are in
         if (blockIdx.x == 0 && tid == 0) {
-            ra.stats[0] = (long long)iter + (long long)__ldcg(&ra.ctr->max_rounds);   // phase-A iterations + longest phase-B ray
+            ra.stats[0] = (long long)iter;
             ra.stats[1] = (long long)__ldcg(&ra.ctr->samples);
-            ra.stats[2] = (long long)__ldcg(&ra.ctr->tiles);
-            ra.stats[3] = (long long)iter;   // iterations that ended in a grid-wide barrier
+            ra.stats[2] = 0;
+            ra.stats[3] = 2 * (long long)iter;   // grid-wide barriers inside the loop
         }
     }
 }
@@ -548,6 +545,7 @@ using namespace ngp;
 // ---------------------------------------------------------------------------------------------- context
 struct ngp_ctx {
     int device = 0, sm_count = 0;
+    size_t max_smem_optin = 0;
     bool has_net = false, has_scene = false;
     NetConst nc{};
     uint2 *wpack = nullptr;
@@ -558,16 +556,17 @@ struct ngp_ctx {
     float min_near = 0.2f;
     // render workspace
     uint32_t capN = 0;
-    float *nears = nullptr, *fars = nullptr, *rays_t = nullptr;
+    float *nears = nullptr, *fars = nullptr, *rays_t = nullptr, *smp_b = nullptr;
+    float4 *smp_a = nullptr;
     int *alive[2] = {nullptr, nullptr};
     RenderCtr *ctr = nullptr;
     // staging for ngp_render_host
     uint32_t capHost = 0;
     float *d_o = nullptr, *d_d = nullptr, *d_img = nullptr, *d_depth = nullptr, *d_ws = nullptr;
+    uint32_t *coarse = nullptr;   // 4x4x4-block occupancy bits, rebuilt from the borrowed bitfield at every ngp_render
+    uint32_t coarse_words = 0;
     long long *prof = nullptr;    // device [8], allocated by ngp_ctx_enable_profile
     int render_blocks = 0, fwd_blocks = 0;
-    int march_budget = 12;        // cell probes per lane per pass (NGP_MARCH_BUDGET)
-    uint32_t lock_schedule = 1;   // NGP_RENDER_NOLOCK=1 keeps every iteration grid-synchronous (debugging / A-B timing)
     size_t render_smem = 0, fwd_smem = 0;
 };
 
@@ -584,19 +583,20 @@ int ngp_ctx_create(ngp_ctx **out) {
     ngp_ctx *c = new ngp_ctx();
     NGP_CUDA(cudaGetDevice(&c->device));
     NGP_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device));
+    {
+        int v = 0;
+        NGP_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
+        c->max_smem_optin = (size_t)v;
+    }
     NGP_CUDA(cudaMalloc(&c->ctr, sizeof(RenderCtr)));
-    const char *nolock = getenv("NGP_RENDER_NOLOCK");
-    c->lock_schedule = (nolock && nolock[0] == '1') ? 0u : 1u;
-    const char *mb = getenv("NGP_MARCH_BUDGET");
-    if (mb && atoi(mb) > 0) c->march_budget = atoi(mb);
     *out = c;
     return 0;
 }
 
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
-    cudaFree(c->wpack); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]);
-    cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
+    cudaFree(c->wpack); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
+    cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
     delete c;
     return 0;
 }
@@ -647,8 +647,8 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
     c->fwd_smem = fwd_smem_bytes(nc);
     c->render_smem = render_smem_bytes(nc);
     NGP_CUDA(cudaFuncSetAttribute(k_network_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_smem));
-    NGP_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem));
-    NGP_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem));
+    NGP_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->max_smem_optin));
+    NGP_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->max_smem_optin));
     int occ = 0;
     NGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_network_forward, kTile, c->fwd_smem));
     NGP_REQUIRE(occ >= 1, "network_forward kernel does not fit on an SM (smem %zu B)", c->fwd_smem);
@@ -687,6 +687,16 @@ int ngp_ctx_set_scene(ngp_ctx *c, const uint8_t *bitfield, uint32_t cascade, uin
     NGP_REQUIRE(aabb_host != nullptr, "ctx_set_scene: aabb_host is null");
     c->bitfield = bitfield; c->cascade = cascade; c->grid_size = grid_size; c->min_near = min_near;
     for (int i = 0; i < 6; i++) c->aabb[i] = aabb_host[i];
+    // coarse occupancy needs 64-cell blocks aligned in Morton order (power-of-two grid) and an 8-byte aligned bitfield
+    const bool pow2 = (grid_size & (grid_size - 1)) == 0 && grid_size >= 32;
+    const uint32_t words = pow2 && (reinterpret_cast<uintptr_t>(bitfield) % 8 == 0) ? cascade * (grid_size * grid_size * grid_size / 2048) : 0;
+    if (words != c->coarse_words) {
+        cudaFree(c->coarse); c->coarse = nullptr; c->coarse_words = 0;
+        if (words) {
+            NGP_CUDA(cudaMalloc(&c->coarse, sizeof(uint32_t) * words));
+            c->coarse_words = words;
+        }
+    }
     c->has_scene = true;
     return 0;
 }
@@ -706,7 +716,7 @@ int ngp_network_forward(ngp_ctx *c, const float *xyzs, const float *dirs, uint32
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     if (N <= c->capN) return 0;
-    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]);
+    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
     c->capN = 0;
     const uint32_t cap = N + N / 8 + 1024;
     NGP_CUDA(cudaMalloc(&c->nears, sizeof(float) * cap));
@@ -714,6 +724,8 @@ static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     NGP_CUDA(cudaMalloc(&c->rays_t, sizeof(float) * cap));
     NGP_CUDA(cudaMalloc(&c->alive[0], sizeof(int) * cap));
     NGP_CUDA(cudaMalloc(&c->alive[1], sizeof(int) * cap));
+    NGP_CUDA(cudaMalloc(&c->smp_a, sizeof(float4) * cap));   // n_alive * n_step <= N rows per iteration
+    NGP_CUDA(cudaMalloc(&c->smp_b, sizeof(float) * cap));
     c->capN = cap;
     return 0;
 }
@@ -728,15 +740,24 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     cudaStream_t st = as_stream(stream);
     NGP_CUDA(cudaMemsetAsync(c->ctr, 0, sizeof(RenderCtr), st));
     RenderArgs ra{};
-    ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps; ra.lock_schedule = c->lock_schedule; ra.march_budget = c->march_budget;
+    ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps;
     for (int i = 0; i < 6; i++) ra.aabb[i] = c->aabb[i];
     ra.mc = make_march_const(c->nc.bound, dt_gamma, max_steps, c->cascade, c->grid_size, c->bitfield);
-    ra.nears = c->nears; ra.fars = c->fars; ra.rays_t = c->rays_t; ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1];
+    ra.nears = c->nears; ra.fars = c->fars; ra.rays_t = c->rays_t; ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1]; ra.smp_a = c->smp_a; ra.smp_b = c->smp_b;
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
+    ra.coarse = nullptr; ra.coarse_words = 0;
+    size_t smem = c->render_smem;
+    if (c->coarse_words && smem + c->coarse_words * 4 <= c->max_smem_optin) {
+        const uint32_t n_blocks = c->coarse_words * 32;
+        k_coarse_occupancy<<<div_up(n_blocks, 256), 256, 0, st>>>(reinterpret_cast<const unsigned long long *>(c->bitfield), n_blocks, c->coarse);
+        if (int rc = after_launch("coarse_occupancy")) return rc;
+        ra.coarse = c->coarse; ra.coarse_words = c->coarse_words;
+        smem += c->coarse_words * 4;
+    }
     NetConst nc = c->nc;
     void *args[] = {&nc, &ra};
-    NGP_CUDA(cudaLaunchCooperativeKernel(c->prof ? (const void *)k_render<true> : (const void *)k_render<false>, dim3(c->render_blocks), dim3(kRenderThreads), args, c->render_smem, st));
+    NGP_CUDA(cudaLaunchCooperativeKernel(c->prof ? (const void *)k_render<true> : (const void *)k_render<false>, dim3(c->render_blocks), dim3(kRenderThreads), args, smem, st));
     return after_launch("render");
 }
 

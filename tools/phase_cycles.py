@@ -17,7 +17,7 @@ import torch  # noqa: E402
 import bench  # noqa: E402
 from nerfsafetyvalidation_b200 import _cabi, synthetic as syn  # noqa: E402
 
-NAMES = ["other(refill,bookkeeping,pro/epilogue)", "march", "row packing", "gather", "mlp", "composite", "grid barrier", "total"]
+NAMES = ["other (tile setup, prologue, epilogue)", "march phase", "barrier after march", "sample load + gather", "mlp", "composite + store + append", "barrier after evaluate", "total"]
 
 
 def main():
@@ -48,11 +48,11 @@ def main():
         _cabi.check(lib.ngp_ctx_phase_cycles(h, buf, 1))
     cyc = np.array(list(buf), dtype=np.float64)
     n_warps = 148 * 16
-    res = {"ms_profiled_launch": e0.elapsed_time(e1), "iterations": stats[0], "samples": stats[1], "passes": stats[2], "barrier_iterations": stats[3],
+    chunks = stats[1] / 32
+    res = {"ms_profiled_launch": e0.elapsed_time(e1), "iterations": stats[0], "samples": stats[1], "grid_barriers": stats[3],
            "phases_pct_of_warp_time": {n: round(100 * c / cyc[7], 2) for n, c in zip(NAMES, cyc)},
            "avg_cycles_per_warp": {n: round(c / n_warps) for n, c in zip(NAMES, cyc)},
-           "cycles_per_pass": {n: round(c / max(stats[2], 1)) for n, c in zip(NAMES[:6], cyc[:6])},
-           "samples_per_pass": stats[1] / max(stats[2], 1)}
+           "warp_cycles_per_32_samples": {n: round(c / chunks) for n, c in zip(NAMES[:7], cyc[:7])}}
     print(json.dumps(res, indent=1))
 
 

@@ -12,9 +12,11 @@ weights, no data-path collective) => weak scaling; `value` = rays of all ranks /
 
 `value`    device-resident inputs, CUDA events around ngp_render on the launching stream, L2 flushed between steps.
 `e2e`      the same frame through ngp_render_host: pinned host rays -> H2D -> render -> D2H image+depth, inside the timer.
-`roofline` dominant kernel = k_render (the only kernel of a step): algorithmic 512 B gathered per sample x samples
-           counted by the kernel, over the measured HBM copy peak (MEASURED_PEAKS.json).  The 2^19 table (23.3 MB fp16)
-           is L2-resident on B200, so frac > 1 is possible and is discussed in DESIGN.md.
+`roofline` dominant kernel = k_render (99.9 % of a step, profiles/): algorithmic 512 B gathered per sample (16 levels x 8
+           corners x 2 ch x 2 B) x samples counted by the kernel, over the measured HBM copy peak
+           (MEASURED_PEAKS.json).  The 2^19 table (23.3 MB fp16) is L2-resident on B200 and every 4-byte corner costs a whole
+           32-byte sector / one L1 wavefront, so the binding roof is the measured random-gather rate (tools/gather_peak.cu,
+           profiles/r01_gather_peak.jsonl: 289 G gathers/s at 16 MB), reported beside it as `roofline.gather`.
 `cpu_baseline`  oracle/ngp_oracle.c (OpenMP port of the reference path) on a strided sub-sample of the same frame.
 `--impl reference`  the same CPU port on all host threads, as the reference arm (the reference has no CPU
            implementation of the NGP path; its CUDA extensions rebuilt for sm_100a are timed beside it as `reference_gpu`).
@@ -45,6 +47,24 @@ WORKLOADS = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch from the committed `ncu --set full` capture
+# (profiles/r01*_k_render_ncu_summary.txt); None where no capture exists
+NCU_DRAM_BYTES_PER_LAUNCH = {"cfg2": 754593024}   # profiles/r01f_k_render_ncu_summary.txt: 403.2 MB read + 351.4 MB written
+
+
+def measured_gather_peak():
+    """G gathers/s of random 4-byte loads from a 16 MB (L2-resident) table, measured by tools/gather_peak.cu."""
+    try:
+        best = 0.0
+        for ln in open(os.path.join(ROOT, "profiles", "r01_gather_peak.jsonl")):
+            d = json.loads(ln)
+            if d["test"] == "random4" and d["table_mb"] == 16.0:
+                best = max(best, d["ggathers_per_s"])
+        return best or None
+    except Exception:
+        return None
+
+
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
@@ -60,16 +80,17 @@ def parse():
 
 
 def frame_rays(wl, rank, n_frames=1):
-    """rays of rank `rank`'s frame(s): cameras on the cfg2 orbit, azimuth advanced per rank/frame (a stand-in for the
-    per-rollout poses of validate.py's disturbance rollouts)."""
-    from nerfsafetyvalidation_b200 import synthetic as syn
-    os_, ds_ = [], []
-    for f in range(n_frames):
-        az = 37.0 + 45.0 * rank + (360.0 / max(n_frames, 1)) * f
-        o, d = syn.pinhole_rays(syn.orbit_pose(az), wl["H"], wl["W"], focal=wl["focal"])
-        os_.append(o)
-        ds_.append(d)
-    return np.concatenate(os_), np.concatenate(ds_)
+    """rays of rank `rank`'s step.  Single frames: cameras on the cfg2 orbit, azimuth advanced per rank.  Rollout batches
+    (cfg3): the first n_frames frames of this rank's disturbance rollouts (rollouts.py: drone dynamics + per-rollout seeded
+    noise + the simulator's pose conversion), i.e. what NerfSimulator would hand to render() during a Monte Carlo run."""
+    from nerfsafetyvalidation_b200 import rollouts as ro, synthetic as syn
+    if n_frames > 1:
+        steps = wl.get("rollout_steps", 20)
+        ids = ro.shard_ids(10 ** 6, rank, max(int(os.environ.get("WORLD_SIZE", "1")), 1))[: -(-n_frames // steps)]
+        o, d, _, _ = ro.rollout_rays(ids, steps, wl["H"], wl["W"], wl["focal"])
+        return np.ascontiguousarray(o[:n_frames].reshape(-1, 3)), np.ascontiguousarray(d[:n_frames].reshape(-1, 3))
+    o, d = syn.pinhole_rays(syn.orbit_pose(37.0 + 45.0 * rank), wl["H"], wl["W"], focal=wl["focal"])
+    return o, d
 
 
 def scene_for(wl):
@@ -284,6 +305,8 @@ def main():
         value = rays_all / (ms_step * 1e-3) / 1e6
         e2e_value = rays_all / (ms_e2e / args.steps * 1e-3) / 1e6
         achieved = samples * 512 / (ms_step * 1e-3) / 1e9    # this rank's kernel: its own samples / its own launch time
+        gather_peak = measured_gather_peak()
+        ggathers = samples * 128 / (ms_step * 1e-3) / 1e9
         line = {"metric": "rendered Mrays/s (NGP hashgrid, cuda_ray inference)", "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
@@ -296,8 +319,12 @@ def main():
                         "api": "ngp_render_host (C ABI, pinned host buffers)"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                             "traffic": None, "kernel": "k_render", "algorithmic_bytes_per_sample": 512,
+                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload), "kernel": "k_render", "algorithmic_bytes_per_sample": 512,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                             "gather": {"achieved_ggathers_per_s": ggathers, "peak_ggathers_per_s": gather_peak,
+                                        "frac": ggathers / gather_peak if gather_peak else None,
+                                        "peak_source": "tools/gather_peak.cu on this pool's B200 (profiles/r01_gather_peak.jsonl): random 4 B "
+                                                       "gathers from a 16 MB L2-resident table"},
                              "tensor_tflops_achieved": samples * 36864 / (ms_step * 1e-3) / 1e12},
                 "clocks": clocks.summary()}
         if world == 1 and not args.no_cpu_baseline:

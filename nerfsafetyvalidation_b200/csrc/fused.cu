@@ -748,7 +748,8 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;
     size_t smem = c->render_smem;
-    if (c->coarse_words && smem + c->coarse_words * 4 <= c->max_smem_optin) {
+    static const bool no_coarse = getenv("NGP_NO_COARSE") != nullptr;   // A/B switch for profiling only
+    if (!no_coarse && c->coarse_words && smem + c->coarse_words * 4 <= c->max_smem_optin) {
         const uint32_t n_blocks = c->coarse_words * 32;
         k_coarse_occupancy<<<div_up(n_blocks, 256), 256, 0, st>>>(reinterpret_cast<const unsigned long long *>(c->bitfield), n_blocks, c->coarse);
         if (int rc = after_launch("coarse_occupancy")) return rc;

@@ -35,14 +35,6 @@ struct NetConst {
     LevelConst lv[kMaxLevels];
 };
 
-struct RenderCtr {
-    uint32_t n_alive[3];    // live rays of iteration k at [k % 3]
-    uint32_t cursor[3];     // MARCH phase: next unclaimed entry of the live list
-    uint32_t ticket[3];     // EVALUATE phase: next unclaimed 32-ray tile
-    uint32_t pad;
-    unsigned long long samples;
-};
-
 // ---------------------------------------------------------------------------------------------- device pieces
 
 __device__ __forceinline__ void copy_wpack_to_smem(const NetConst &nc, uint2 *s_w) {
@@ -249,34 +241,56 @@ k_network_forward(NetConst nc, const float *__restrict__ xyzs, const float *__re
 
 // ---------------------------------------------------------------------------------------------- persistent renderer
 // NeRFRenderer.run_cuda's inference loop (nerf/renderer.py:329-376) as ONE persistent cooperative launch, one 16-warp CTA per
-// SM.  The reference's global schedule `n_step = clamp(N // n_alive, 1, 8)` (renderer.py:357) is kept exactly -- per-ray sample
-// counts and the rays_t recurrence depend on it -- so the grid meets twice per iteration:
+// SM.  The reference's global schedule `n_step = clamp(N // n_alive, 1, 8)` (renderer.py:357) decides where every ray's
+// chunks end, and a chunk boundary is visible in the result (rays_t restarts from the compositor's sum of deltas), so the
+// schedule is reproduced exactly -- but not by meeting once per iteration.  Two facts make that unnecessary:
 //
+//   (1) given the schedule, a ray is independent of every other ray, and the marcher does not need the network: the value the
+//       compositor writes back to rays_t is rays_t + the fp32 sum of the chunk's deltas[:,1] (raymarching.cu:870-905), which
+//       the marcher can accumulate itself.  So one march call can emit E chunks of s samples with the restart applied at
+//       every chunk boundary, bit for bit what E reference iterations with n_step = s would have emitted.
+//   (2) n_alive never grows, so n_step never shrinks: the schedule is seven thresholds.  An EPOCH runs E reference iterations
+//       speculating that n_step stays s; every ray reports the iteration it died in (ran out of samples: known to the
+//       marcher; T < 1e-4: found by the compositor) into a histogram, from which every CTA recomputes n_alive of each of the
+//       E iterations after the epoch's barrier.  If n_step would have changed at iteration j < E, the epoch is REPLAYED from
+//       the committed ray state with E = j (exact by construction); otherwise its results are committed.  E is chosen from
+//       the distance to the next threshold and the last observed death rate, so replays are rare; they cost time, never
+//       correctness.
+//
+// Per epoch, two phases separated by a grid barrier (2 barriers per epoch instead of 2 per reference iteration):
 //   MARCH     lane-level dynamic scheduling: every LANE owns one live ray, probes the occupancy bitfield one cell per trip in
-//             lockstep with the other 31 lanes of its warp (so the warp stays converged whatever mix of occupied / empty cells
-//             its rays cross), and the moment its ray has its n_step samples (or leaves the box) the lane takes the next live
-//             ray from the list (warp ballot + prefix, one atomic per warp per refill).  Samples go to an L2-resident buffer in
-//             the reference's row order (row = n * n_step + s, raymarching.cu:732-734): 20 B per sample, no dirs.
-//   EVALUATE  warp w pulls tiles of 32 live rays = 32 * n_step consecutive sample rows (consecutive rows are consecutive samples
-//   + COMPOSITE  of one ray and share hash-grid cells): 16-level gather -> sigma MLP -> SH + colour MLP, 32 rows at a time on
-//             tensor cores with the weights resident in shared memory; then lane r composites ray r front to back in registers
-//             with early termination (raymarching.cu:828-913) and the survivors are appended to the next live list with one
-//             ballot + one atomicAdd per warp (list order is not the reference's, which no per-ray output depends on; the
-//             stand-alone compact_alive op keeps the stable order).
-// xyz / deltas make one trip through L2; dirs / sigmas / rgbs never exist in memory.
+//             lockstep with the other 31 lanes of its warp, and the moment its ray has its E*s samples (or left the box) the
+//             lane takes the next live ray from the list.  Samples go to a streaming buffer (20 B per sample, evict-first)
+//             laid out per 32-ray tile as [sample i][ray r] so the evaluator reads it fully coalesced.
+//   EVALUATE  a warp pulls a tile of 32 consecutive live rays (adjacent pixels: their samples share hash-grid cells) and walks
+//   + COMPOSITE  their samples in lockstep, pass i = sample i of each ray: 16-level gather -> sigma MLP -> SH + colour MLP on
+//             tensor cores with the weights resident in shared memory, then lane r composites its sample into the ray
+//             accumulators it holds in registers for the whole epoch (raymarching.cu:828-913), early termination included.
+//             Ray state makes one 32-byte round trip per EPOCH; dirs / sigmas / rgbs never exist in memory.
 constexpr int kRenderThreads = 512;
 constexpr int kRenderWarps = kRenderThreads / 32;
 constexpr int kMaxStep = 8;                    // renderer.py:357
-constexpr int kTileRows = 32 * kMaxStep;       // sample rows of one 32-ray tile
+constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
 constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
 
+struct EpochCtr {
+    uint32_t cursor;            // MARCH phase: next unclaimed entry of the live list
+    uint32_t ticket;            // EVALUATE phase: next unclaimed 32-ray tile
+    uint32_t n_out;             // survivors appended to the next live list
+    uint32_t pad;
+    uint32_t hist[kMaxEpoch];   // rays that died in iteration j of the epoch
+};
+struct RenderCtr {
+    EpochCtr e[3];              // attempt a uses e[a % 3]; e[(a + 1) % 3] is zeroed during attempt a
+    unsigned long long samples;
+    uint32_t error;
+};
+
 struct WarpSmem {
-    float sigma[kTileRows], rg[kTileRows], b[kTileRows];   // network outputs per row (rg = half2 bits: rgb are half-rounded)
-    float dt[kTileRows], dl[kTileRows];                    // deltas[:, 0], deltas[:, 1]
     __half enc[32 * kEncStride];               // A-operand staging of the current 32 rows; first 16 B of a row = (sigma, r, g, b) after the MLPs
     __half sh[32 * kShStride];                 // degree-4 SH of lane r's ray direction
 };
-static_assert(sizeof(WarpSmem) % 16 == 0 && offsetof(WarpSmem, enc) % 16 == 0 && offsetof(WarpSmem, sh) % 16 == 0, "WarpSmem alignment");
+static_assert(sizeof(WarpSmem) % 16 == 0 && offsetof(WarpSmem, sh) % 16 == 0, "WarpSmem alignment");
 
 struct RenderArgs {
     const float *rays_o, *rays_d;
@@ -285,12 +299,16 @@ struct RenderArgs {
     uint32_t max_steps;
     float aabb[6];
     MarchConst mc;
-    float *nears, *fars, *rays_t;
+    float *nears, *fars;
+    float4 *state[2];  // [2 N] per buffer: (t, weights_sum, depth, seq) , (r, g, b, samples); committed / tentative ping-pong
     int *alive[2];
+    uint32_t *n_emit;  // [N] samples the marcher emitted for live-list entry n in this epoch
     const uint32_t *coarse;   // [coarse_words] 4x4x4-block occupancy bits (Morton order) or NULL
     uint32_t coarse_words;
-    float4 *smp_a;     // [N] (x, y, z, dt) per sample row of the current iteration
-    float *smp_b;      // [N] t_new - last_t
+    float4 *smp_a;     // [cap_rows] (x, y, z, dt) per sample of the current epoch
+    float *smp_b;      // [cap_rows] t_new - last_t
+    uint32_t cap_rows;
+    uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -298,13 +316,19 @@ struct RenderArgs {
     long long *prof;   // optional [8]: warp-cycles per phase (diagnostics, ngp_ctx_phase_cycles)
 };
 
-// MARCH phase of one iteration for one warp (see the header comment).  Returns the samples this lane emitted.
-__device__ __forceinline__ uint32_t march_phase(const RenderArgs &ra, const uint32_t *s_coarse, int lane, uint32_t lt_mask,
-                                                const int *__restrict__ alive_in, uint32_t n_alive, uint32_t n_step, uint32_t *cursor) {
+__device__ __forceinline__ uint32_t clamp_n_step(uint32_t N, uint32_t n_alive) {   // renderer.py:357
+    const uint32_t q = N / n_alive;
+    return q > (uint32_t)kMaxStep ? (uint32_t)kMaxStep : (q < 1u ? 1u : q);
+}
+
+// MARCH phase of one epoch for one warp (see the header comment): up to ES = E * s samples per live ray, in chunks of s.
+__device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t *s_coarse, int lane, uint32_t lt_mask,
+                                            const int *__restrict__ alive_in, const float4 *__restrict__ state_in, uint32_t n_alive,
+                                            uint32_t s, uint32_t ES, uint32_t *cursor) {
     bool has = false, list_done = false;
-    uint32_t n = 0, emitted = 0, total = 0;
-    int index = 0;
-    float ox = 0.f, oy = 0.f, oz = 0.f, tm = 0.f, last_t = 0.f, far = 0.f;
+    uint32_t n = 0, emitted = 0, in_chunk = 0;
+    size_t row = 0;
+    float ox = 0.f, oy = 0.f, oz = 0.f, tm = 0.f, last_t = 0.f, far = 0.f, acc_t = 0.f;
     RayDir rd = make_ray_dir(1.f, 1.f, 1.f);
     for (;;) {
         const uint32_t need = __ballot_sync(0xffffffffu, !has);
@@ -317,14 +341,15 @@ __device__ __forceinline__ uint32_t march_phase(const RenderArgs &ra, const uint
                 const uint32_t my = start + (uint32_t)__popc(need & lt_mask);
                 if (my < n_alive) {
                     n = my;
-                    index = __ldcg(alive_in + n);
+                    const int index = __ldcg(alive_in + n);
                     const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
                     ox = __ldg(o); oy = __ldg(o + 1); oz = __ldg(o + 2);
                     rd = make_ray_dir(__ldg(d), __ldg(d + 1), __ldg(d + 2));
-                    tm = __ldcg(ra.rays_t + index);
-                    last_t = tm;
+                    tm = __ldcg(reinterpret_cast<const float *>(state_in + 2 * (size_t)index));   // rays_t
+                    last_t = tm; acc_t = tm;
                     far = __ldcg(ra.fars + index);
-                    emitted = 0;
+                    emitted = 0; in_chunk = 0;
+                    row = (size_t)(n >> 5) * 32 * ES + (n & 31u);
                     has = true;
                 }
             }
@@ -337,112 +362,132 @@ __device__ __forceinline__ uint32_t march_phase(const RenderArgs &ra, const uint
         if (has) {   // one lockstep probe
             float x, y, z, dt, dl;
             if (tm < far && march_probe(ra.mc, ox, oy, oz, rd, tm, last_t, x, y, z, dt, dl, s_coarse)) {
-                const size_t row = (size_t)n * n_step + emitted;
-                __stcg(ra.smp_a + row, make_float4(x, y, z, dt));
-                __stcg(ra.smp_b + row, dl);
+                __stcs(ra.smp_a + row, make_float4(x, y, z, dt));
+                __stcs(ra.smp_b + row, dl);
+                row += 32;
                 emitted++;
-            }
-            if (emitted == n_step || !(tm < far)) {      // chunk complete (raymarching.cu:752) or ray exhausted
-                for (uint32_t s = emitted; s < n_step; s++) {   // un-emitted rows read as delta == 0 (raymarching.py:329-331)
-                    const size_t row = (size_t)n * n_step + s;
-                    __stcg(ra.smp_a + row, make_float4(0.f, 0.f, 0.f, 0.f));
-                    __stcg(ra.smp_b + row, 0.f);
+                acc_t = __fadd_rn(acc_t, dl);           // what composite_rays will store to rays_t (raymarching.cu:870,905)
+                if (++in_chunk == s) {                  // chunk boundary: the next march call starts from rays_t (:723-725)
+                    in_chunk = 0;
+                    tm = acc_t; last_t = acc_t;
                 }
-                if (ra.samples_per_ray && emitted) ra.samples_per_ray[index] += (int)emitted;
-                total += emitted;
+            }
+            if (emitted == ES || !(tm < far)) {         // epoch complete (raymarching.cu:752) or ray exhausted
+                __stcg(ra.n_emit + n, emitted);
                 has = false;
             }
         }
         __syncwarp();
     }
-    return total;
 }
 
-// EVALUATE + COMPOSITE phase of one iteration for one warp (see the header comment).
+// EVALUATE + COMPOSITE phase of one epoch for one warp (see the header comment).
 template <bool kProf>
 __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs &ra, const uint2 *__restrict__ s_w, WarpSmem &ws, int lane,
-                                           uint32_t lt_mask, const int *__restrict__ alive_in, int *__restrict__ alive_out, uint32_t n_alive,
-                                           uint32_t n_step, uint32_t *ticket, uint32_t *next_count, long long (&pc)[8]) {
+                                           uint32_t lt_mask, const int *__restrict__ alive_in, int *__restrict__ alive_out,
+                                           const float4 *__restrict__ state_in, float4 *__restrict__ state_out, uint32_t n_alive,
+                                           uint32_t s, uint32_t ES, uint32_t seq, EpochCtr *ec, uint32_t *s_hist, long long (&pc)[8]) {
     const uint32_t n_tiles = (n_alive + 31) / 32;
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
     uint32_t next_tile = 0;
-    if (lane == 0) next_tile = atomicAdd(ticket, 1u);
+    if (lane == 0) next_tile = atomicAdd(&ec->ticket, 1u);
+    next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
+    int nx_index = 0;
+    uint32_t nx_ne = 0;
+    if (next_tile < n_tiles && next_tile * 32 + lane < n_alive) {
+        nx_index = __ldcg(alive_in + next_tile * 32 + lane);
+        nx_ne = __ldcg(ra.n_emit + next_tile * 32 + lane);
+    }
     for (;;) {
-        const uint32_t tile = __shfl_sync(0xffffffffu, next_tile, 0);
+        const uint32_t tile = next_tile;
         if (tile >= n_tiles) break;
-        if (lane == 0) next_tile = atomicAdd(ticket, 1u);   // claimed now, needed a whole tile later: its latency is hidden
-        const uint32_t n = tile * 32 + lane;
-        const bool has_ray = n < n_alive;
-        int index = 0;
+        const bool has_ray = tile * 32 + lane < n_alive;
+        const int index = nx_index;
+        const uint32_t ne = has_ray ? nx_ne : 0u;
+        if (lane == 0) next_tile = atomicAdd(&ec->ticket, 1u);   // claimed now, read after the first pass: its latency is hidden
+        bool fetched_next = false;
+        const size_t tbase = (size_t)tile * 32 * ES + lane;
+        float4 sa = make_float4(0.f, 0.f, 0.f, 0.f);
+        float sb = 0.f;
+        if (ne > 0) { sa = __ldcs(ra.smp_a + tbase); sb = __ldcs(ra.smp_b + tbase); }
         RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        uint32_t samples = 0;
         if (has_ray) {
-            index = __ldcg(alive_in + n);
+            const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
             const float *d = ra.rays_d + (size_t)index * 3;
             uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + lane * kShStride);
             sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), srow[0], srow[1]);   // the direction is constant along the ray
-            a.t = __ldcg(ra.rays_t + index); a.ws = __ldcg(ra.weights_sum + index); a.d = __ldcg(ra.depth + index);
-            a.r = __ldcg(ra.image + (size_t)index * 3); a.g = __ldcg(ra.image + (size_t)index * 3 + 1); a.b = __ldcg(ra.image + (size_t)index * 3 + 2);
+            a.t = r0.x; a.ws = r0.y; a.d = r0.z; a.r = r1.x; a.g = r1.y; a.b = r1.z;
+            samples = __float_as_uint(r1.w);
         }
-        const uint32_t tile_rays = min(32u, n_alive - tile * 32);
-        const uint32_t rows = tile_rays * n_step;
-        const size_t row_base = (size_t)tile * 32 * n_step;
+        uint32_t max_ne = ne;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) max_ne = max(max_ne, __shfl_xor_sync(0xffffffffu, max_ne, o));
+        bool dead = false;
+        uint32_t death = 0;          // iteration of the epoch this ray died in
+        uint32_t chunk = 0, in_chunk = 0;
         NGP_PROF(0)
-        for (uint32_t row0 = 0; row0 < rows; row0 += 32) {
-            const uint32_t r = row0 + lane;
-            float4 sa = make_float4(0.f, 0.f, 0.f, 0.f);
-            float sb = 0.f;
-            if (r < rows) {
-                sa = __ldcg(ra.smp_a + row_base + r);
-                sb = __ldcg(ra.smp_b + row_base + r);
-            }
-            ws.dt[r] = sa.w; ws.dl[r] = sb;
-            const bool live = sa.w != 0.f;                       // delta == 0 is the reference's end-of-ray sentinel
-            if (live) encode_point(nc, sa.x, sa.y, sa.z, reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
+        for (uint32_t i = 0; i < max_ne; i++) {
+            const bool active = !dead && i < ne;
+            if (!__any_sync(0xffffffffu, active)) break;
+            const float4 ca = sa;
+            const float cb = sb;
+            if (!dead && i + 1 < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i + 1) * 32); sb = __ldcs(ra.smp_b + tbase + (size_t)(i + 1) * 32); }
+            if (active) encode_point(nc, ca.x, ca.y, ca.z, reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
             __syncwarp();
             NGP_PROF(3)
-            if (__any_sync(0xffffffffu, live)) {
-                mlp_rows32(nc, s_w, ws.enc,
-                           [&](int rr) {
-                               const uint32_t ray = min((row0 + (uint32_t)rr) / n_step, 31u);
-                               return ws.sh + ray * kShStride;
-                           },
-                           0, lane, [&](int rr, float sg) { reinterpret_cast<float *>(ws.enc + rr * kEncStride)[0] = sg; },
-                           [&](int rr, int t, float v0, float v1) {
-                               float *o = reinterpret_cast<float *>(ws.enc + rr * kEncStride);
-                               if (t == 0) { o[1] = v0; o[2] = v1; } else { o[3] = v0; }
-                           });
-                __syncwarp();
-                if (live) {
-                    const float4 o = *reinterpret_cast<const float4 *>(ws.enc + lane * kEncStride);
-                    ws.sigma[r] = o.x; ws.rg[r] = __uint_as_float(pack_half2(o.y, o.z)); ws.b[r] = o.w;   // rgb are half-rounded: exact
+            mlp_rows32(nc, s_w, ws.enc, [&](int rr) { return ws.sh + rr * kShStride; }, 0, lane,
+                       [&](int rr, float sg) { reinterpret_cast<float *>(ws.enc + rr * kEncStride)[0] = sg; },
+                       [&](int rr, int t, float v0, float v1) {
+                           float *o = reinterpret_cast<float *>(ws.enc + rr * kEncStride);
+                           if (t == 0) { o[1] = v0; o[2] = v1; } else { o[3] = v0; }
+                       });
+            __syncwarp();
+            if (active) {   // composite (raymarching.cu:866-894)
+                const float4 o = *reinterpret_cast<const float4 *>(ws.enc + lane * kEncStride);
+                if (composite_sample(a, o.x, o.y, o.z, o.w, ca.w, cb)) {
+                    dead = true;
+                    death = chunk;
+                    samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
+                }
+            }
+            if (++in_chunk == s) { in_chunk = 0; chunk++; }
+            if (!fetched_next) {   // the next tile's list entries, one tile ahead of their use
+                fetched_next = true;
+                next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
+                if (next_tile < n_tiles && next_tile * 32 + lane < n_alive) {
+                    nx_index = __ldcg(alive_in + next_tile * 32 + lane);
+                    nx_ne = __ldcg(ra.n_emit + next_tile * 32 + lane);
                 }
             }
             __syncwarp();
             NGP_PROF(4)
         }
-        // ---- composite (raymarching.cu:828-913): lane r <-> ray r, rows r * n_step .. + n_step - 1
+        if (!fetched_next) {
+            next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
+            if (next_tile < n_tiles && next_tile * 32 + lane < n_alive) {
+                nx_index = __ldcg(alive_in + next_tile * 32 + lane);
+                nx_ne = __ldcg(ra.n_emit + next_tile * 32 + lane);
+            }
+        }
+        // ---- end of the epoch for these rays: who survives (raymarching.cu:896-911), tentative state, next live list
         bool survives = false;
         if (has_ray) {
-            uint32_t s = 0;
-            while (s < n_step) {
-                const uint32_t r = lane * n_step + s;
-                const float dt = ws.dt[r];
-                if (dt == 0.f) break;
-                const uint32_t rg = __float_as_uint(ws.rg[r]);
-                const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&rg));
-                if (composite_sample(a, ws.sigma[r], c.x, c.y, ws.b[r], dt, ws.dl[r])) break;
-                s++;
+            if (!dead) {
+                samples += ne;
+                if (ne < ES) { dead = true; death = ne / s; }   // the chunk that came up short: delta == 0 sentinel (:860-863)
+                else survives = true;
             }
-            survives = s == n_step;
-            if (survives) __stcg(ra.rays_t + index, a.t);                       // raymarching.cu:905-911
-            __stcg(ra.weights_sum + index, a.ws); __stcg(ra.depth + index, a.d);
-            __stcg(ra.image + (size_t)index * 3, a.r); __stcg(ra.image + (size_t)index * 3 + 1, a.g); __stcg(ra.image + (size_t)index * 3 + 2, a.b);
+            if (dead) atomicAdd(s_hist + death, 1u);
+            float4 *so = state_out + 2 * (size_t)index;
+            __stcg(so, make_float4(a.t, a.ws, a.d, __uint_as_float(seq)));
+            __stcg(so + 1, make_float4(a.r, a.g, a.b, __uint_as_float(samples)));
         }
         const uint32_t ballot = __ballot_sync(0xffffffffu, survives);   // renderer.py:369
         if (ballot) {
             uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(next_count, (uint32_t)__popc(ballot));
+            if (lane == 0) base = atomicAdd(&ec->n_out, (uint32_t)__popc(ballot));
             base = __shfl_sync(0xffffffffu, base, 0);
             if (survives) __stcg(alive_out + base + __popc(ballot & lt_mask), index);
         }
@@ -456,6 +501,7 @@ template <bool kProf>
 __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, RenderArgs ra) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch];
     uint2 *s_w = reinterpret_cast<uint2 *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpSmem &ws = reinterpret_cast<WarpSmem *>(s_w + nc.wpack_count)[warp];
@@ -467,6 +513,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     copy_wpack_to_smem(nc, s_w);
     if (s_coarse)
         for (uint32_t i = tid; i < ra.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(ra.coarse + i);
+    if (tid < kMaxEpoch) s_hist[tid] = 0;
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
@@ -474,51 +521,107 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         float near, far;
         if (!slab_near_far(__ldg(o), __ldg(o + 1), __ldg(o + 2), __ldg(d), __ldg(d + 1), __ldg(d + 2), ra.aabb, ra.min_near, near, far))
             near = far = FLT_MAX;
-        ra.nears[n] = near; ra.fars[n] = far; ra.rays_t[n] = near;
+        ra.nears[n] = near; ra.fars[n] = far;
         ra.alive[0][n] = (int)n;
-        ra.weights_sum[n] = 0.f; ra.depth[n] = 0.f;
-        ra.image[(size_t)n * 3] = 0.f; ra.image[(size_t)n * 3 + 1] = 0.f; ra.image[(size_t)n * 3 + 2] = 0.f;
-        if (ra.samples_per_ray) ra.samples_per_ray[n] = 0;
+        ra.state[0][2 * (size_t)n] = make_float4(near, 0.f, 0.f, __uint_as_float(1u));
+        ra.state[0][2 * (size_t)n + 1] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+        ra.state[1][2 * (size_t)n] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
     }
-    if (blockIdx.x == 0 && tid == 0) ra.ctr->n_alive[0] = N;   // all counters were zeroed by the host before the launch
     grid.sync();
 
-    uint32_t step = 0, iter = 0, tot_emitted = 0;
-    while (step < ra.max_steps) {
-        const uint32_t n_alive = __ldcg(&ra.ctr->n_alive[iter % 3]);
-        if (n_alive == 0) break;
-        uint32_t n_step = N / n_alive;                                  // renderer.py:357
-        n_step = n_step > kMaxStep ? kMaxStep : (n_step < 1 ? 1 : n_step);
-        const int *alive_in = ra.alive[iter & 1];
-        int *alive_out = ra.alive[(iter & 1) ^ 1];
-        const uint32_t slot = iter % 3, nslot = (iter + 1) % 3;
-        if (blockIdx.x == 0 && tid == 0) {   // none of these words is touched by anyone else during this iteration
-            ra.ctr->cursor[nslot] = 0;
-            ra.ctr->ticket[nslot] = 0;
-            ra.ctr->n_alive[(iter + 2) % 3] = 0;
+    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = N, E = 1, replays = 0;
+    bool replay = false;
+    while (step < ra.max_steps && n_alive > 0) {
+        const uint32_t s = clamp_n_step(N, n_alive);                         // renderer.py:357
+        if (!replay) {
+            if (s >= (uint32_t)kMaxStep) E = kMaxEpoch;                      // n_alive only shrinks: n_step stays 8
+            else {
+                const uint32_t margin = n_alive - N / (s + 1);               // deaths until N // n_alive reaches s + 1
+                const uint32_t rate = last_rate < 1u ? 1u : last_rate;
+                const uint32_t e = margin / (2u * rate);
+                E = e < 1u ? 1u : (e > (uint32_t)kMaxEpoch ? (uint32_t)kMaxEpoch : e);
+            }
+            if (ra.max_epoch && E > ra.max_epoch) E = ra.max_epoch;
         }
+        {
+            const uint32_t left = (ra.max_steps - step + s - 1) / s;         // iterations the `while step < max_steps` loop still allows
+            if (E > left) E = left;
+            const uint32_t fit = ra.cap_rows / (((n_alive + 31u) & ~31u) * s);   // sample-buffer capacity
+            if (E > fit) E = fit < 1u ? 1u : fit;
+        }
+        const uint32_t ES = E * s;
+        EpochCtr *ec = &ra.ctr->e[attempt % 3];
+        if (blockIdx.x == 0 && tid < (int)(sizeof(EpochCtr) / 4))   // nobody else touches this slot during this attempt
+            reinterpret_cast<uint32_t *>(&ra.ctr->e[(attempt + 1) % 3])[tid] = 0;
+        const int *alive_in = ra.alive[in];
+        int *alive_out = ra.alive[in ^ 1];
+        const float4 *state_in = ra.state[in];
+        float4 *state_out = ra.state[in ^ 1];
         long long g0 = kProf ? clock64() : 0;
-        tot_emitted += march_phase(ra, s_coarse, lane, lt_mask, alive_in, n_alive, n_step, &ra.ctr->cursor[slot]);
+        march_phase(ra, s_coarse, lane, lt_mask, alive_in, state_in, n_alive, s, ES, &ec->cursor);
         if (kProf) { const long long g1 = clock64(); pc[1] += g1 - g0; g0 = g1; }
         grid.sync();
         if (kProf) pc[2] += clock64() - g0;
-        eval_phase<kProf>(nc, ra, s_w, ws, lane, lt_mask, alive_in, alive_out, n_alive, n_step, &ra.ctr->ticket[slot], &ra.ctr->n_alive[nslot], pc);
+        eval_phase<kProf>(nc, ra, s_w, ws, lane, lt_mask, alive_in, alive_out, state_in, state_out, n_alive, s, ES, attempt + 2, ec, s_hist, pc);
         if (kProf) g0 = clock64();
+        __syncthreads();
+        if (tid < kMaxEpoch) {
+            const uint32_t v = s_hist[tid];
+            if (v) atomicAdd(&ec->hist[tid], v);
+            s_hist[tid] = 0;
+        }
         grid.sync();
+        if (tid < kMaxEpoch) s_val[tid] = tid < (int)E ? __ldcg(&ec->hist[tid]) : 0u;
+        __syncthreads();
+        // ---- validate the speculation: replay the reference's schedule over the epoch's death histogram
+        uint32_t na = n_alive, ran = 0, last = 0;
+        bool ok = true;
+        for (uint32_t j = 0; j < E; j++) {
+            if (j > 0) {
+                if (na == 0) break;                                         // renderer.py:352-353: the loop ended here
+                if (clamp_n_step(N, na) != s) { ok = false; break; }        // n_step changed: iterations >= j ran with the wrong chunking
+            }
+            last = s_val[j];
+            na -= last;
+            ran++;
+        }
+        __syncthreads();   // s_val is rewritten after the next epoch
         if (kProf) pc[6] += clock64() - g0;
-        step += n_step;
-        iter++;
+        attempt++;
+        if (!ok) {          // replay from the committed state with the E that is known to be valid
+            E = ran;
+            replay = true;
+            replays++;
+            continue;
+        }
+        if (blockIdx.x == 0 && tid == 0 && __ldcg(&ec->n_out) != na) ra.ctr->error = 1;   // histogram and live list disagree
+        replay = false;
+        step += ran * s;
+        iter += ran;
+        last_rate = last;
+        n_alive = na;
+        in ^= 1;
     }
 
-    // ---- epilogue: background + depth normalisation (renderer.py:375-376); all accumulators are final after the last barrier
+    // ---- epilogue: background + depth normalisation (renderer.py:375-376) from the newest record of every ray
+    uint32_t my_samples = 0;
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
-        const float ws_n = __ldcg(ra.weights_sum + n);
+        float4 r0 = __ldcg(ra.state[0] + 2 * (size_t)n);
+        const float4 q0 = __ldcg(ra.state[1] + 2 * (size_t)n);
+        const bool second = __float_as_uint(q0.w) > __float_as_uint(r0.w);
+        if (second) r0 = q0;
+        const float4 r1 = __ldcg(ra.state[second ? 1 : 0] + 2 * (size_t)n + 1);
+        const float ws_n = r0.y;
         const float k = __fmul_rn(__fsub_rn(1.0f, ws_n), ra.bg_color);
         float *im = ra.image + (size_t)n * 3;
-        im[0] = __fadd_rn(__ldcg(im), k); im[1] = __fadd_rn(__ldcg(im + 1), k); im[2] = __fadd_rn(__ldcg(im + 2), k);
+        im[0] = __fadd_rn(r1.x, k); im[1] = __fadd_rn(r1.y, k); im[2] = __fadd_rn(r1.z, k);
+        ra.weights_sum[n] = ws_n;
         const float near = ra.nears[n], far = ra.fars[n];
-        const float dd = __fsub_rn(__ldcg(ra.depth + n), near);
+        const float dd = __fsub_rn(r0.z, near);
         ra.depth[n] = __fdiv_rn(dd < 0.f ? 0.f : dd, __fsub_rn(far, near));   // 0/0 = NaN for misses, like the reference
+        const uint32_t cnt = __float_as_uint(r1.w);
+        if (ra.samples_per_ray) ra.samples_per_ray[n] = (int)cnt;
+        my_samples += cnt;
     }
     if (kProf && lane == 0) {
         pc[7] = clock64() - k_start;
@@ -526,14 +629,14 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         for (int k = 0; k < 8; k++) atomicAdd(reinterpret_cast<unsigned long long *>(ra.prof + k), (unsigned long long)pc[k]);
     }
     if (ra.stats) {
-        const uint32_t wemit = warp_sum(tot_emitted);
-        if (lane == 0) atomicAdd(&ra.ctr->samples, (unsigned long long)wemit);
+        const uint32_t wsum = warp_sum(my_samples);
+        if (lane == 0) atomicAdd(&ra.ctr->samples, (unsigned long long)wsum);
         grid.sync();   // every warp's counters are in
         if (blockIdx.x == 0 && tid == 0) {
             ra.stats[0] = (long long)iter;
             ra.stats[1] = (long long)__ldcg(&ra.ctr->samples);
-            ra.stats[2] = 0;
-            ra.stats[3] = 2 * (long long)iter;   // grid-wide barriers inside the loop
+            ra.stats[2] = __ldcg(&ra.ctr->error) ? -1ll : (long long)attempt;   // epochs run (replays included); -1 = internal inconsistency
+            ra.stats[3] = (long long)replays;
         }
     }
 }
@@ -556,8 +659,10 @@ struct ngp_ctx {
     float min_near = 0.2f;
     // render workspace
     uint32_t capN = 0;
-    float *nears = nullptr, *fars = nullptr, *rays_t = nullptr, *smp_b = nullptr;
-    float4 *smp_a = nullptr;
+    uint32_t capRows = 0;
+    float *nears = nullptr, *fars = nullptr, *smp_b = nullptr;
+    float4 *smp_a = nullptr, *state[2] = {nullptr, nullptr};
+    uint32_t *n_emit = nullptr;
     int *alive[2] = {nullptr, nullptr};
     RenderCtr *ctr = nullptr;
     // staging for ngp_render_host
@@ -567,7 +672,7 @@ struct ngp_ctx {
     uint32_t coarse_words = 0;
     long long *prof = nullptr;    // device [8], allocated by ngp_ctx_enable_profile
     int render_blocks = 0, fwd_blocks = 0;
-    size_t render_smem = 0, fwd_smem = 0;
+    size_t render_smem = 0, render_smem_max = 0, fwd_smem = 0;
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
@@ -595,7 +700,8 @@ int ngp_ctx_create(ngp_ctx **out) {
 
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
-    cudaFree(c->wpack); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
+    cudaFree(c->wpack); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
+    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
     cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
     delete c;
     return 0;
@@ -647,8 +753,13 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
     c->fwd_smem = fwd_smem_bytes(nc);
     c->render_smem = render_smem_bytes(nc);
     NGP_CUDA(cudaFuncSetAttribute(k_network_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_smem));
-    NGP_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->max_smem_optin));
-    NGP_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->max_smem_optin));
+    {
+        cudaFuncAttributes fa;
+        NGP_CUDA(cudaFuncGetAttributes(&fa, k_render<false>));
+        c->render_smem_max = c->max_smem_optin - fa.sharedSizeBytes;   // dynamic part: opt-in limit minus the kernel's static arrays
+        NGP_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem_max));
+        NGP_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->render_smem_max));
+    }
     int occ = 0;
     NGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_network_forward, kTile, c->fwd_smem));
     NGP_REQUIRE(occ >= 1, "network_forward kernel does not fit on an SM (smem %zu B)", c->fwd_smem);
@@ -716,17 +827,28 @@ int ngp_network_forward(ngp_ctx *c, const float *xyzs, const float *dirs, uint32
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     if (N <= c->capN) return 0;
-    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->rays_t); cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
+    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
+    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
     c->capN = 0;
     const uint32_t cap = N + N / 8 + 1024;
+    // sample buffer of one epoch: rows_per_ray * N rows of 20 B (streamed, evict-first); >= N + 256 rows always fits one iteration
+    static const char *rpr_env = getenv("NGP_ROWS_PER_RAY");
+    unsigned long long rpr = rpr_env ? strtoull(rpr_env, nullptr, 10) : 16ull;
+    if (rpr < 1) rpr = 1;
+    unsigned long long rows = rpr * cap + 1024;
+    if (rows > 0x7fffffffull) rows = 0x7fffffffull;
+    NGP_REQUIRE(rows >= (unsigned long long)N + 256, "render: %u rays do not fit the sample buffer", N);
     NGP_CUDA(cudaMalloc(&c->nears, sizeof(float) * cap));
     NGP_CUDA(cudaMalloc(&c->fars, sizeof(float) * cap));
-    NGP_CUDA(cudaMalloc(&c->rays_t, sizeof(float) * cap));
+    NGP_CUDA(cudaMalloc(&c->state[0], sizeof(float4) * 2 * (size_t)cap));
+    NGP_CUDA(cudaMalloc(&c->state[1], sizeof(float4) * 2 * (size_t)cap));
+    NGP_CUDA(cudaMalloc(&c->n_emit, sizeof(uint32_t) * cap));
     NGP_CUDA(cudaMalloc(&c->alive[0], sizeof(int) * cap));
     NGP_CUDA(cudaMalloc(&c->alive[1], sizeof(int) * cap));
-    NGP_CUDA(cudaMalloc(&c->smp_a, sizeof(float4) * cap));   // n_alive * n_step <= N rows per iteration
-    NGP_CUDA(cudaMalloc(&c->smp_b, sizeof(float) * cap));
+    NGP_CUDA(cudaMalloc(&c->smp_a, sizeof(float4) * (size_t)rows));
+    NGP_CUDA(cudaMalloc(&c->smp_b, sizeof(float) * (size_t)rows));
     c->capN = cap;
+    c->capRows = (uint32_t)rows;
     return 0;
 }
 
@@ -743,13 +865,16 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps;
     for (int i = 0; i < 6; i++) ra.aabb[i] = c->aabb[i];
     ra.mc = make_march_const(c->nc.bound, dt_gamma, max_steps, c->cascade, c->grid_size, c->bitfield);
-    ra.nears = c->nears; ra.fars = c->fars; ra.rays_t = c->rays_t; ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1]; ra.smp_a = c->smp_a; ra.smp_b = c->smp_b;
+    ra.nears = c->nears; ra.fars = c->fars; ra.state[0] = c->state[0]; ra.state[1] = c->state[1]; ra.n_emit = c->n_emit;
+    ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1]; ra.smp_a = c->smp_a; ra.smp_b = c->smp_b; ra.cap_rows = c->capRows;
+    static const char *me_env = getenv("NGP_MAX_EPOCH");   // A/B switch for profiling only: 1 = one barrier pair per reference iteration
+    ra.max_epoch = me_env ? (uint32_t)strtoul(me_env, nullptr, 10) : 0u;
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;
     size_t smem = c->render_smem;
     static const bool no_coarse = getenv("NGP_NO_COARSE") != nullptr;   // A/B switch for profiling only
-    if (!no_coarse && c->coarse_words && smem + c->coarse_words * 4 <= c->max_smem_optin) {
+    if (!no_coarse && c->coarse_words && smem + c->coarse_words * 4 <= c->render_smem_max) {
         const uint32_t n_blocks = c->coarse_words * 32;
         k_coarse_occupancy<<<div_up(n_blocks, 256), 256, 0, st>>>(reinterpret_cast<const unsigned long long *>(c->bitfield), n_blocks, c->coarse);
         if (int rc = after_launch("coarse_occupancy")) return rc;

@@ -49,7 +49,7 @@ def main():
     cyc = np.array(list(buf), dtype=np.float64)
     n_warps = 148 * 16
     chunks = stats[1] / 32
-    res = {"ms_profiled_launch": e0.elapsed_time(e1), "iterations": stats[0], "samples": stats[1], "grid_barriers": stats[3],
+    res = {"ms_profiled_launch": e0.elapsed_time(e1), "iterations": stats[0], "samples": stats[1], "epochs": stats[2], "replays": stats[3],
            "phases_pct_of_warp_time": {n: round(100 * c / cyc[7], 2) for n, c in zip(NAMES, cyc)},
            "avg_cycles_per_warp": {n: round(c / n_warps) for n, c in zip(NAMES, cyc)},
            "warp_cycles_per_32_samples": {n: round(c / chunks) for n, c in zip(NAMES[:7], cyc[:7])}}

@@ -312,7 +312,7 @@ __device__ __forceinline__ void sh_basis(float x, float y, float z, uint32_t deg
 // ------------------------------------------------------------------------------------------------
 // Tensor-core MLP building blocks: mma.sync.m16n8k16 f16 x f16 -> f32, activations chained in registers.
 __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile(
+    asm(
         "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
         : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
@@ -331,18 +331,28 @@ template <int MT, int KT, int NT>
 __device__ __forceinline__ void mlp_layer(const uint32_t (&A)[MT][KT][4], const uint2 *__restrict__ wf, int lane,
                                           float (&C)[MT][NT][4]) {
 #pragma unroll
-    for (int nt = 0; nt < NT; nt++) {
+    for (int nt = 0; nt < NT; nt++)
 #pragma unroll
         for (int mt = 0; mt < MT; mt++) {
             C[mt][nt][0] = 0.f; C[mt][nt][1] = 0.f; C[mt][nt][2] = 0.f; C[mt][nt][3] = 0.f;
         }
+    // k-tile outermost: the MT * NT accumulators are independent, so back-to-back mma never wait on each other
 #pragma unroll
-        for (int kt = 0; kt < KT; kt++) {
+    for (int kt = 0; kt < KT; kt++) {
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
             const uint2 b = wf[(nt * KT + kt) * 32 + lane];
 #pragma unroll
             for (int mt = 0; mt < MT; mt++) mma16816(C[mt][nt], A[mt][kt], b.x, b.y);
         }
     }
+}
+
+// relu + round-to-nearest fp16 pair in one instruction (lo -> low half)
+__device__ __forceinline__ uint32_t pack_half2_relu(float lo, float hi) {
+    uint32_t d;
+    asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
 }
 
 // ReLU + fp16 rounding; accumulators of a 64-wide layer become the next layer's A fragments.
@@ -352,10 +362,10 @@ __device__ __forceinline__ void relu_to_frag(const float (&C)[MT][NT][4], uint32
     for (int mt = 0; mt < MT; mt++)
 #pragma unroll
         for (int kt = 0; kt < NT / 2; kt++) {
-            A[mt][kt][0] = pack_half2(fmaxf(C[mt][2 * kt][0], 0.f), fmaxf(C[mt][2 * kt][1], 0.f));
-            A[mt][kt][1] = pack_half2(fmaxf(C[mt][2 * kt][2], 0.f), fmaxf(C[mt][2 * kt][3], 0.f));
-            A[mt][kt][2] = pack_half2(fmaxf(C[mt][2 * kt + 1][0], 0.f), fmaxf(C[mt][2 * kt + 1][1], 0.f));
-            A[mt][kt][3] = pack_half2(fmaxf(C[mt][2 * kt + 1][2], 0.f), fmaxf(C[mt][2 * kt + 1][3], 0.f));
+            A[mt][kt][0] = pack_half2_relu(C[mt][2 * kt][0], C[mt][2 * kt][1]);
+            A[mt][kt][1] = pack_half2_relu(C[mt][2 * kt][2], C[mt][2 * kt][3]);
+            A[mt][kt][2] = pack_half2_relu(C[mt][2 * kt + 1][0], C[mt][2 * kt + 1][1]);
+            A[mt][kt][3] = pack_half2_relu(C[mt][2 * kt + 1][2], C[mt][2 * kt + 1][3]);
         }
 }
 

@@ -271,6 +271,7 @@ constexpr int kRenderThreads = 512;
 constexpr int kRenderWarps = kRenderThreads / 32;
 constexpr int kMaxStep = 8;                    // renderer.py:357
 constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
+constexpr int kMaxSamplesPerEpoch = 128;      // E * s cap: bounds the longest tile of an epoch
 constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
 
 struct EpochCtr {
@@ -279,6 +280,7 @@ struct EpochCtr {
     uint32_t n_out;             // survivors appended to the next live list
     uint32_t pad;
     uint32_t hist[kMaxEpoch];   // rays that died in iteration j of the epoch
+    uint32_t mhist[kMaxEpoch];  // of those, the ones that ran out of samples -- known to the marcher, before anything is evaluated
 };
 struct RenderCtr {
     EpochCtr e[3];              // attempt a uses e[a % 3]; e[(a + 1) % 3] is zeroed during attempt a
@@ -309,6 +311,7 @@ struct RenderArgs {
     float *smp_b;      // [cap_rows] t_new - last_t
     uint32_t cap_rows;
     uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
+    uint32_t force_kshift;   // >= 4: automatic; else log2 of the samples per ray per evaluation pass (profiling A/B)
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -321,13 +324,27 @@ __device__ __forceinline__ uint32_t clamp_n_step(uint32_t N, uint32_t n_alive) {
     return q > (uint32_t)kMaxStep ? (uint32_t)kMaxStep : (q < 1u ? 1u : q);
 }
 
+// Tile geometry of one epoch: a tile is R = 32 / K consecutive live rays, one evaluation pass covers K consecutive samples of
+// each (lane = r * K + k).  K = 1 is "32 adjacent pixels, one sample each"; K = 8 gives 8x more (and 8x shorter) tiles, which is
+// what keeps 2368 warps evenly loaded once few rays are left.  Sample rows of a tile are stored [pass][ray][k], so a pass reads
+// 32 consecutive rows.
+struct TileGeom {
+    uint32_t kshift;   // log2 K
+    uint32_t ESp;      // samples per ray rounded up to a multiple of K (row slots per ray)
+};
+__device__ __forceinline__ size_t sample_row0(const TileGeom &tg, uint32_t n) {
+    const uint32_t rshift = 5u - tg.kshift;
+    return (size_t)(n >> rshift) * ((32u >> tg.kshift) * tg.ESp) + ((n & ((1u << rshift) - 1u)) << tg.kshift);
+}
+
 // MARCH phase of one epoch for one warp (see the header comment): up to ES = E * s samples per live ray, in chunks of s.
 __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t *s_coarse, int lane, uint32_t lt_mask,
                                             const int *__restrict__ alive_in, const float4 *__restrict__ state_in, uint32_t n_alive,
-                                            uint32_t s, uint32_t ES, uint32_t *cursor) {
+                                            uint32_t s, uint32_t ES, const TileGeom tg, uint32_t *cursor, uint32_t *s_hist) {
     bool has = false, list_done = false;
     uint32_t n = 0, emitted = 0, in_chunk = 0;
-    size_t row = 0;
+    const uint32_t kmask = (1u << tg.kshift) - 1u;
+    size_t row0 = 0;
     float ox = 0.f, oy = 0.f, oz = 0.f, tm = 0.f, last_t = 0.f, far = 0.f, acc_t = 0.f;
     RayDir rd = make_ray_dir(1.f, 1.f, 1.f);
     for (;;) {
@@ -349,7 +366,7 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
                     last_t = tm; acc_t = tm;
                     far = __ldcg(ra.fars + index);
                     emitted = 0; in_chunk = 0;
-                    row = (size_t)(n >> 5) * 32 * ES + (n & 31u);
+                    row0 = sample_row0(tg, n);
                     has = true;
                 }
             }
@@ -362,9 +379,9 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
         if (has) {   // one lockstep probe
             float x, y, z, dt, dl;
             if (tm < far && march_probe(ra.mc, ox, oy, oz, rd, tm, last_t, x, y, z, dt, dl, s_coarse)) {
+                const size_t row = row0 + (size_t)(emitted >> tg.kshift) * 32 + (emitted & kmask);
                 __stcs(ra.smp_a + row, make_float4(x, y, z, dt));
                 __stcs(ra.smp_b + row, dl);
-                row += 32;
                 emitted++;
                 acc_t = __fadd_rn(acc_t, dl);           // what composite_rays will store to rays_t (raymarching.cu:870,905)
                 if (++in_chunk == s) {                  // chunk boundary: the next march call starts from rays_t (:723-725)
@@ -374,6 +391,7 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
             }
             if (emitted == ES || !(tm < far)) {         // epoch complete (raymarching.cu:752) or ray exhausted
                 __stcg(ra.n_emit + n, emitted);
+                if (emitted < ES) atomicAdd(s_hist + emitted / s, 1u);   // dies in the chunk that came up short (:860-863)
                 has = false;
             }
         }
@@ -386,8 +404,14 @@ template <bool kProf>
 __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs &ra, const uint2 *__restrict__ s_w, WarpSmem &ws, int lane,
                                            uint32_t lt_mask, const int *__restrict__ alive_in, int *__restrict__ alive_out,
                                            const float4 *__restrict__ state_in, float4 *__restrict__ state_out, uint32_t n_alive,
-                                           uint32_t s, uint32_t ES, uint32_t seq, EpochCtr *ec, uint32_t *s_hist, long long (&pc)[8]) {
-    const uint32_t n_tiles = (n_alive + 31) / 32;
+                                           uint32_t s, uint32_t ES, const TileGeom tg, uint32_t seq, EpochCtr *ec, uint32_t *s_hist,
+                                           long long (&pc)[8]) {
+    const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
+    const uint32_t n_tiles = (n_alive + R - 1) / R;
+    const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
+    const bool leader = my_k == 0;
+    const int lead_lane = lane & ~(int)(K - 1u);
+    const size_t tile_rows = (size_t)R * tg.ESp;
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
     uint32_t next_tile = 0;
@@ -395,28 +419,28 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
     next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
     int nx_index = 0;
     uint32_t nx_ne = 0;
-    if (next_tile < n_tiles && next_tile * 32 + lane < n_alive) {
-        nx_index = __ldcg(alive_in + next_tile * 32 + lane);
-        nx_ne = __ldcg(ra.n_emit + next_tile * 32 + lane);
+    if (next_tile < n_tiles && next_tile * R + my_r < n_alive) {
+        nx_index = __ldcg(alive_in + next_tile * R + my_r);
+        nx_ne = __ldcg(ra.n_emit + next_tile * R + my_r);
     }
     for (;;) {
         const uint32_t tile = next_tile;
         if (tile >= n_tiles) break;
-        const bool has_ray = tile * 32 + lane < n_alive;
+        const bool has_ray = tile * R + my_r < n_alive;
         const int index = nx_index;
-        const uint32_t ne = has_ray ? nx_ne : 0u;
+        const uint32_t ne = has_ray ? min(nx_ne, ES) : 0u;       // ES may be shorter than what was marched (pre-validated epoch)
         if (lane == 0) next_tile = atomicAdd(&ec->ticket, 1u);   // claimed now, read after the first pass: its latency is hidden
         bool fetched_next = false;
-        const size_t tbase = (size_t)tile * 32 * ES + lane;
+        const size_t tbase = (size_t)tile * tile_rows + lane;
         float4 sa = make_float4(0.f, 0.f, 0.f, 0.f);
         float sb = 0.f;
-        if (ne > 0) { sa = __ldcs(ra.smp_a + tbase); sb = __ldcs(ra.smp_b + tbase); }
+        if (my_k < ne) { sa = __ldcs(ra.smp_a + tbase); sb = __ldcs(ra.smp_b + tbase); }
         RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         uint32_t samples = 0;
-        if (has_ray) {
+        if (has_ray && leader) {
             const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
             const float *d = ra.rays_d + (size_t)index * 3;
-            uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + lane * kShStride);
+            uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + my_r * kShStride);
             sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), srow[0], srow[1]);   // the direction is constant along the ray
             a.t = r0.x; a.ws = r0.y; a.d = r0.z; a.r = r1.x; a.g = r1.y; a.b = r1.z;
             samples = __float_as_uint(r1.w);
@@ -424,41 +448,53 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
         uint32_t max_ne = ne;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) max_ne = max(max_ne, __shfl_xor_sync(0xffffffffu, max_ne, o));
-        bool dead = false;
-        uint32_t death = 0;          // iteration of the epoch this ray died in
-        uint32_t chunk = 0, in_chunk = 0;
+        bool dead = false;           // the ray of this lane (leader decides, group follows)
+        uint32_t death = 0;          // leader: iteration of the epoch this ray died in
+        uint32_t chunk = 0, in_chunk = 0;   // leader: position of the next sample in the reference's chunking
         NGP_PROF(0)
-        for (uint32_t i = 0; i < max_ne; i++) {
+        for (uint32_t i0 = 0; i0 < max_ne; i0 += K) {
+            const uint32_t i = i0 + my_k;
             const bool active = !dead && i < ne;
             if (!__any_sync(0xffffffffu, active)) break;
             const float4 ca = sa;
             const float cb = sb;
-            if (!dead && i + 1 < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i + 1) * 32); sb = __ldcs(ra.smp_b + tbase + (size_t)(i + 1) * 32); }
-            if (active) encode_point(nc, ca.x, ca.y, ca.z, reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
+            if (!dead && i + K < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i0 + K) * R); sb = __ldcs(ra.smp_b + tbase + (size_t)(i0 + K) * R); }
+            if (active) {
+                encode_point(nc, ca.x, ca.y, ca.z, reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
+                *reinterpret_cast<float2 *>(ws.enc + lane * kEncStride + 32) = make_float2(ca.w, cb);   // (dt, delta_t) in the row's pad
+            }
             __syncwarp();
             NGP_PROF(3)
-            mlp_rows32(nc, s_w, ws.enc, [&](int rr) { return ws.sh + rr * kShStride; }, 0, lane,
+            mlp_rows32(nc, s_w, ws.enc, [&](int rr) { return ws.sh + ((uint32_t)rr >> kshift) * kShStride; }, 0, lane,
                        [&](int rr, float sg) { reinterpret_cast<float *>(ws.enc + rr * kEncStride)[0] = sg; },
                        [&](int rr, int t, float v0, float v1) {
                            float *o = reinterpret_cast<float *>(ws.enc + rr * kEncStride);
                            if (t == 0) { o[1] = v0; o[2] = v1; } else { o[3] = v0; }
                        });
             __syncwarp();
-            if (active) {   // composite (raymarching.cu:866-894)
-                const float4 o = *reinterpret_cast<const float4 *>(ws.enc + lane * kEncStride);
-                if (composite_sample(a, o.x, o.y, o.z, o.w, ca.w, cb)) {
-                    dead = true;
-                    death = chunk;
-                    samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
+            if (leader && has_ray && !dead) {   // composite this pass's <= K samples of the ray in order (raymarching.cu:866-894)
+                const uint32_t cnt = min(K, ne - min(ne, i0));
+                for (uint32_t k = 0; k < cnt; k++) {
+                    const __half *row = ws.enc + (lane + k) * kEncStride;
+                    const float4 o = *reinterpret_cast<const float4 *>(row);
+                    const float2 dd = *reinterpret_cast<const float2 *>(row + 32);
+                    const bool term = composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y);
+                    if (term) {
+                        dead = true;
+                        death = chunk;
+                        samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
+                        break;
+                    }
+                    if (++in_chunk == s) { in_chunk = 0; chunk++; }
                 }
             }
-            if (++in_chunk == s) { in_chunk = 0; chunk++; }
+            if (K > 1) dead = __shfl_sync(0xffffffffu, dead, lead_lane);
             if (!fetched_next) {   // the next tile's list entries, one tile ahead of their use
                 fetched_next = true;
                 next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
-                if (next_tile < n_tiles && next_tile * 32 + lane < n_alive) {
-                    nx_index = __ldcg(alive_in + next_tile * 32 + lane);
-                    nx_ne = __ldcg(ra.n_emit + next_tile * 32 + lane);
+                if (next_tile < n_tiles && next_tile * R + my_r < n_alive) {
+                    nx_index = __ldcg(alive_in + next_tile * R + my_r);
+                    nx_ne = __ldcg(ra.n_emit + next_tile * R + my_r);
                 }
             }
             __syncwarp();
@@ -466,14 +502,14 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
         }
         if (!fetched_next) {
             next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
-            if (next_tile < n_tiles && next_tile * 32 + lane < n_alive) {
-                nx_index = __ldcg(alive_in + next_tile * 32 + lane);
-                nx_ne = __ldcg(ra.n_emit + next_tile * 32 + lane);
+            if (next_tile < n_tiles && next_tile * R + my_r < n_alive) {
+                nx_index = __ldcg(alive_in + next_tile * R + my_r);
+                nx_ne = __ldcg(ra.n_emit + next_tile * R + my_r);
             }
         }
         // ---- end of the epoch for these rays: who survives (raymarching.cu:896-911), tentative state, next live list
         bool survives = false;
-        if (has_ray) {
+        if (has_ray && leader) {
             if (!dead) {
                 samples += ne;
                 if (ne < ES) { dead = true; death = ne / s; }   // the chunk that came up short: delta == 0 sentinel (:860-863)
@@ -546,10 +582,24 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         {
             const uint32_t left = (ra.max_steps - step + s - 1) / s;         // iterations the `while step < max_steps` loop still allows
             if (E > left) E = left;
-            const uint32_t fit = ra.cap_rows / (((n_alive + 31u) & ~31u) * s);   // sample-buffer capacity
-            if (E > fit) E = fit < 1u ? 1u : fit;
+            const uint32_t cap = (uint32_t)kMaxSamplesPerEpoch / s;         // bounds the longest tile (load balance)
+            if (E > cap) E = cap < 1u ? 1u : cap;
+            const uint32_t g = s == 8 ? 1u : (s == 4 ? 2u : (s == 2 || s == 6 ? 4u : 8u));   // E * s a multiple of 8 once it can be
+            if (E >= g) E -= E % g;
         }
-        const uint32_t ES = E * s;
+        uint32_t ES;
+        TileGeom tg;
+        for (;;) {   // tile geometry; shrink the epoch until its samples fit the buffer (rarely more than one trip)
+            ES = E * s;
+            tg.kshift = ra.force_kshift < 4u ? ra.force_kshift : (ES >= 5u ? 3u : (ES >= 3u ? 2u : ES - 1u));   // K = 8, 4, 2, 1
+            tg.ESp = (ES + (1u << tg.kshift) - 1u) & ~((1u << tg.kshift) - 1u);
+            const uint32_t R = 32u >> tg.kshift;
+            unsigned long long rows = (unsigned long long)((n_alive + R - 1) / R) * R * tg.ESp;
+            if (rows <= ra.cap_rows) break;
+            if (E > 1) { E = E > 8u ? E - 8u : E - 1u; continue; }
+            tg.kshift = 0; tg.ESp = ES;   // one iteration, no padding: (n_alive + 31) * s <= N + 248 rows always fits
+            break;
+        }
         EpochCtr *ec = &ra.ctr->e[attempt % 3];
         if (blockIdx.x == 0 && tid < (int)(sizeof(EpochCtr) / 4))   // nobody else touches this slot during this attempt
             reinterpret_cast<uint32_t *>(&ra.ctr->e[(attempt + 1) % 3])[tid] = 0;
@@ -558,11 +608,32 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         const float4 *state_in = ra.state[in];
         float4 *state_out = ra.state[in ^ 1];
         long long g0 = kProf ? clock64() : 0;
-        march_phase(ra, s_coarse, lane, lt_mask, alive_in, state_in, n_alive, s, ES, &ec->cursor);
+        march_phase(ra, s_coarse, lane, lt_mask, alive_in, state_in, n_alive, s, ES, tg, &ec->cursor, s_hist);
         if (kProf) { const long long g1 = clock64(); pc[1] += g1 - g0; g0 = g1; }
+        __syncthreads();
+        if (tid < kMaxEpoch) {
+            const uint32_t v = s_hist[tid];
+            if (v) atomicAdd(&ec->mhist[tid], v);
+            s_hist[tid] = 0;
+        }
         grid.sync();
+        // ---- pre-validation: the rays that ran out of samples are known now.  If they alone move n_step at iteration j, only
+        //      the first j iterations of what was marched are evaluated (the marched samples of those are exact).
+        if (tid < kMaxEpoch) s_val[tid] = tid < (int)E ? __ldcg(&ec->mhist[tid]) : 0u;
+        __syncthreads();
+        {
+            uint32_t na = n_alive, ok_iters = 0;
+            for (uint32_t j = 0; j < E; j++) {
+                if (j > 0 && (na == 0 || clamp_n_step(N, na) != s)) break;
+                na -= s_val[j];
+                ok_iters++;
+            }
+            E = ok_iters;
+            ES = E * s;
+        }
+        __syncthreads();   // s_val is rewritten below
         if (kProf) pc[2] += clock64() - g0;
-        eval_phase<kProf>(nc, ra, s_w, ws, lane, lt_mask, alive_in, alive_out, state_in, state_out, n_alive, s, ES, attempt + 2, ec, s_hist, pc);
+        eval_phase<kProf>(nc, ra, s_w, ws, lane, lt_mask, alive_in, alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, pc);
         if (kProf) g0 = clock64();
         __syncthreads();
         if (tid < kMaxEpoch) {
@@ -833,8 +904,8 @@ static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     const uint32_t cap = N + N / 8 + 1024;
     // sample buffer of one epoch: rows_per_ray * N rows of 20 B (streamed, evict-first); >= N + 256 rows always fits one iteration
     static const char *rpr_env = getenv("NGP_ROWS_PER_RAY");
-    unsigned long long rpr = rpr_env ? strtoull(rpr_env, nullptr, 10) : 16ull;
-    if (rpr < 1) rpr = 1;
+    unsigned long long rpr = rpr_env ? strtoull(rpr_env, nullptr, 10) : 32ull;
+    if (rpr < 2) rpr = 2;
     unsigned long long rows = rpr * cap + 1024;
     if (rows > 0x7fffffffull) rows = 0x7fffffffull;
     NGP_REQUIRE(rows >= (unsigned long long)N + 256, "render: %u rays do not fit the sample buffer", N);
@@ -869,6 +940,8 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1]; ra.smp_a = c->smp_a; ra.smp_b = c->smp_b; ra.cap_rows = c->capRows;
     static const char *me_env = getenv("NGP_MAX_EPOCH");   // A/B switch for profiling only: 1 = one barrier pair per reference iteration
     ra.max_epoch = me_env ? (uint32_t)strtoul(me_env, nullptr, 10) : 0u;
+    static const char *ks_env = getenv("NGP_KSHIFT");
+    ra.force_kshift = ks_env ? (uint32_t)strtoul(ks_env, nullptr, 10) : 4u;
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;

@@ -121,6 +121,9 @@ int ngp_ctx_phase_cycles(ngp_ctx *ctx, int64_t *out_host, int reset);
  * Any M >= 0 (rows padded internally). */
 int ngp_network_forward(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint32_t M, int apply_density_scale,
                         float *sigmas, float *rgbs, void *stream);
+/* Same contract as ngp_network_forward, both MLPs on tcgen05 (128-row tiles, accumulators in tensor memory). */
+int ngp_network_forward_tc(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint32_t M, int apply_density_scale,
+                           float *sigmas, float *rgbs, void *stream);
 /* NeRFRenderer.run_cuda, inference branch (nerf/renderer.py:261-284,329-386) as ONE persistent launch:
  * near/far -> loop{march -> encode -> MLPs -> composite -> stable compaction, global n_step schedule} ->
  * background mix + depth normalisation.  image [N,3], depth [N], weights_sum [N] fp32 (any may not be NULL).

@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "device_math.cuh"
 #include "scan.cuh"
+#include "tc_mlp.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -30,6 +31,8 @@ struct NetConst {
     const __half2 *table;
     const uint2 *wpack;            // global, fragment order: sigma net then colour net
     uint32_t wpack_count;          // uint2 elements
+    const uint4 *wtc;              // global, tcgen05 operand order (tc_mlp.cuh), sigma net then colour net
+    uint32_t wtc_bytes;
     uint32_t nh_sigma, nh_color;   // hidden (64x64) matmuls per net = num_layers - 1
     float bound, two_bound, density_scale;
     LevelConst lv[kMaxLevels];
@@ -44,13 +47,14 @@ __device__ __forceinline__ void copy_wpack_to_smem(const NetConst &nc, uint2 *s_
 }
 
 // 16-level hash-grid encoding of one point into 16 half2 (= 4 x uint4) of shared memory.
-__device__ __forceinline__ void encode_point(const NetConst &nc, float x, float y, float z, uint4 *dst) {
+// dst[g * stride], g = 0..3, receives levels 4g .. 4g+3 (8 halves).
+__device__ __forceinline__ void encode_point(const NetConst &nc, float x, float y, float z, uint4 *dst, int stride = 1) {
     // grid.py:144  inputs = (inputs + bound) / (2 * bound)
     const float u0 = __fdiv_rn(__fadd_rn(x, nc.bound), nc.two_bound);
     const float u1 = __fdiv_rn(__fadd_rn(y, nc.bound), nc.two_bound);
     const float u2 = __fdiv_rn(__fadd_rn(z, nc.bound), nc.two_bound);
     if ((u0 < 0 || u0 > 1) || (u1 < 0 || u1 > 1) || (u2 < 0 || u2 > 1)) {  // gridencoder.cu:99-123
-        dst[0] = dst[1] = dst[2] = dst[3] = make_uint4(0, 0, 0, 0);
+        dst[0] = dst[stride] = dst[2 * stride] = dst[3 * stride] = make_uint4(0, 0, 0, 0);
         return;
     }
     // 4 levels (32 independent 4-byte gathers) per trip; the trip loop is deliberately NOT unrolled: the renderer's 16 warps
@@ -88,7 +92,7 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
             }
             packed[j] = pack_half2(a0, a1);
         }
-        dst[grp] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        dst[grp * stride] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
     }
 }
 
@@ -237,6 +241,67 @@ k_network_forward(NetConst nc, const float *__restrict__ xyzs, const float *__re
                    });
         __syncwarp();
     }
+}
+
+// ---------------------------------------------------------------------------------------------- tcgen05 variants
+__global__ void k_pack_network_tc(const __half *__restrict__ w_sigma, uint32_t nh_sigma, const __half *__restrict__ w_color,
+                                  uint32_t nh_color, uint4 *__restrict__ dst) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const tc::WeightMap wm = tc::weight_map(nh_sigma, nh_color);
+    unsigned char *base = reinterpret_cast<unsigned char *>(dst);
+    tc::pack_weight_chunks(w_sigma, 64, 32, reinterpret_cast<uint4 *>(base + wm.s0), tid, nt, false);
+    for (uint32_t k = 0; k < nh_sigma; k++)
+        tc::pack_weight_chunks(w_sigma + 2048 + (size_t)k * 4096, 64, 64, reinterpret_cast<uint4 *>(base + wm.sh + k * 8192), tid, nt, false);
+    tc::pack_weight_chunks(w_sigma + 2048 + (size_t)nh_sigma * 4096, 16, 64, reinterpret_cast<uint4 *>(base + wm.sl), tid, nt, false);
+    tc::pack_weight_chunks(w_color, 64, 32, reinterpret_cast<uint4 *>(base + wm.c0), tid, nt, true);
+    for (uint32_t k = 0; k < nh_color; k++)
+        tc::pack_weight_chunks(w_color + 2048 + (size_t)k * 4096, 64, 64, reinterpret_cast<uint4 *>(base + wm.ch + k * 8192), tid, nt, false);
+    tc::pack_weight_chunks(w_color + 2048 + (size_t)nh_color * 4096, 16, 64, reinterpret_cast<uint4 *>(base + wm.cl), tid, nt, false);
+}
+
+// network_ff.py:51-74 with both MLPs on tcgen05: one warpgroup per CTA, thread = row of a 128-row tile.
+__global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const float *__restrict__ xyzs, const float *__restrict__ dirs, uint32_t M,
+                                                            float *__restrict__ sigmas, float *__restrict__ rgbs, uint32_t n_tiles) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
+    uint4 *s_a = s_w + nc.wtc_bytes / 16;
+    uint64_t *s_mbar = reinterpret_cast<uint64_t *>(s_a + 8 * tc::kRows);
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_mbar + 1);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (uint32_t i = tid; i < nc.wtc_bytes / 16; i += blockDim.x) s_w[i] = __ldg(nc.wtc + i);
+    tc::fence_async_smem();
+    if (warp == 0) tc::tmem_alloc(tc::smem_u32(s_tmem), tc::kTmemColsPerTile);
+    if (tid == 0) {
+        tc::mbar_init(tc::smem_u32(s_mbar), 1);
+        tc::mbar_init_fence();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(s_tmem);
+    tc::Tile t;
+    t.a = s_a; t.a_saddr = tc::smem_u32(s_a); t.w_saddr = tc::smem_u32(s_w); t.mbar_saddr = tc::smem_u32(s_mbar);
+    t.tmem = tmem_base + ((uint32_t)(warp * 32) << 16); t.bar_id = 1; t.parity = 0;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint32_t row = tile * tc::kRows + tid;
+        uint4 sh_lo = make_uint4(0, 0, 0, 0), sh_hi = sh_lo;
+        if (row < M) {
+            encode_point(nc, __ldg(xyzs + (size_t)row * 3), __ldg(xyzs + (size_t)row * 3 + 1), __ldg(xyzs + (size_t)row * 3 + 2), s_a + tid, tc::kRows);
+            sh_to_half(__ldg(dirs + (size_t)row * 3), __ldg(dirs + (size_t)row * 3 + 1), __ldg(dirs + (size_t)row * 3 + 2), sh_lo, sh_hi);
+        } else {
+            s_a[tid] = s_a[tc::kRows + tid] = s_a[2 * tc::kRows + tid] = s_a[3 * tc::kRows + tid] = make_uint4(0, 0, 0, 0);
+        }
+        float sg, r, g, b;
+        tc::mlp_tile128(t, tid, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, r, g, b);
+        if (row < M) {
+            sigmas[row] = sg;
+            float *o = rgbs + (size_t)row * 3;
+            o[0] = r; o[1] = g; o[2] = b;
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem_base, tc::kTmemColsPerTile);
 }
 
 // ---------------------------------------------------------------------------------------------- persistent renderer
@@ -723,6 +788,7 @@ struct ngp_ctx {
     bool has_net = false, has_scene = false;
     NetConst nc{};
     uint2 *wpack = nullptr;
+    uint4 *wtc = nullptr;
     // scene
     const uint8_t *bitfield = nullptr;
     uint32_t cascade = 1, grid_size = 128;
@@ -743,7 +809,7 @@ struct ngp_ctx {
     uint32_t coarse_words = 0;
     long long *prof = nullptr;    // device [8], allocated by ngp_ctx_enable_profile
     int render_blocks = 0, fwd_blocks = 0;
-    size_t render_smem = 0, render_smem_max = 0, fwd_smem = 0;
+    size_t render_smem = 0, render_smem_max = 0, fwd_smem = 0, fwd_tc_smem = 0;
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
@@ -771,7 +837,7 @@ int ngp_ctx_create(ngp_ctx **out) {
 
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
-    cudaFree(c->wpack); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
+    cudaFree(c->wpack); cudaFree(c->wtc); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
     cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
     cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
     delete c;
@@ -821,6 +887,18 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
     if (int rc = after_launch("pack_network")) return rc;
     nc.wpack = c->wpack;
     nc.wpack_count = count;
+    {
+        const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
+        if (c->wtc) { cudaFree(c->wtc); c->wtc = nullptr; }
+        NGP_CUDA(cudaMalloc(&c->wtc, wm.total));
+        k_pack_network_tc<<<1, 256, 0, st>>>(reinterpret_cast<const __half *>(w_sigma_f16), nc.nh_sigma, reinterpret_cast<const __half *>(w_color_f16),
+                                             nc.nh_color, c->wtc);
+        if (int rc = after_launch("pack_network_tc")) return rc;
+        nc.wtc = c->wtc;
+        nc.wtc_bytes = wm.total;
+        c->fwd_tc_smem = wm.total + 8 * tc::kRows * 16 + 16;
+        NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
+    }
     c->fwd_smem = fwd_smem_bytes(nc);
     c->render_smem = render_smem_bytes(nc);
     NGP_CUDA(cudaFuncSetAttribute(k_network_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_smem));
@@ -894,6 +972,20 @@ int ngp_network_forward(ngp_ctx *c, const float *xyzs, const float *dirs, uint32
     if (!apply_density_scale) nc.density_scale = 1.0f;
     k_network_forward<<<grid, kTile, c->fwd_smem, as_stream(stream)>>>(nc, xyzs, dirs, M, sigmas, rgbs, n_tiles);
     return after_launch("network_forward");
+}
+
+int ngp_network_forward_tc(ngp_ctx *c, const float *xyzs, const float *dirs, uint32_t M, int apply_density_scale, float *sigmas,
+                           float *rgbs, void *stream) {
+    NGP_REQUIRE(c != nullptr && c->has_net, "network_forward_tc: ngp_ctx_set_network has not been called");
+    if (M == 0) return 0;
+    NGP_DEVPTR(xyzs); NGP_DEVPTR(dirs); NGP_DEVPTR(sigmas); NGP_DEVPTR(rgbs);
+    const uint32_t n_tiles = div_up(M, (uint32_t)tc::kRows);
+    const uint32_t cap = (uint32_t)c->sm_count * 4;
+    const uint32_t grid = n_tiles < cap ? n_tiles : cap;
+    NetConst nc = c->nc;
+    if (!apply_density_scale) nc.density_scale = 1.0f;
+    k_network_forward_tc<<<grid, tc::kRows, c->fwd_tc_smem, as_stream(stream)>>>(nc, xyzs, dirs, M, sigmas, rgbs, n_tiles);
+    return after_launch("network_forward_tc");
 }
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {

@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "_lib", "libngp_b200.so")
+LIB_PATH = os.environ.get("NGP_B200_LIB") or os.path.join(_PKG, "_lib", "libngp_b200.so")   # the override is for A/B builds only
 
 _u32, _f32, _i32, _p, _u64 = C.c_uint32, C.c_float, C.c_int, C.c_void_p, C.c_uint64
 

@@ -36,6 +36,7 @@ struct NetConst {
     uint32_t nh_sigma, nh_color;   // hidden (64x64) matmuls per net = num_layers - 1
     float bound, two_bound, density_scale;
     LevelConst lv[kMaxLevels];
+    const __half2 *lvbase[kMaxLevels];   // table + lv[l].offset: one 64-bit base per level, 32-bit row offsets in the gather
 };
 
 // ---------------------------------------------------------------------------------------------- device pieces
@@ -70,7 +71,7 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
             float p0 = __fmaf_rn(u0, scale, 0.5f), p1 = __fmaf_rn(u1, scale, 0.5f), p2 = __fmaf_rn(u2, scale, 0.5f);
             const uint32_t g0 = (uint32_t)floorf(p0), g1 = (uint32_t)floorf(p1), g2 = (uint32_t)floorf(p2);
             f[j][0] = __fsub_rn(p0, (float)g0); f[j][1] = __fsub_rn(p1, (float)g1); f[j][2] = __fsub_rn(p2, (float)g2);
-            const __half2 *tl = nc.table + lc.offset;
+            const __half2 *tl = nc.lvbase[grp * 4 + j];
             uint32_t row[8];
             cell_rows(lc, g0, g1, g2, row);
 #pragma unroll
@@ -332,8 +333,14 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
 //             tensor cores with the weights resident in shared memory, then lane r composites its sample into the ray
 //             accumulators it holds in registers for the whole epoch (raymarching.cu:828-913), early termination included.
 //             Ray state makes one 32-byte round trip per EPOCH; dirs / sigmas / rgbs never exist in memory.
-constexpr int kRenderThreads = 512;
+#ifndef NGP_RENDER_THREADS
+#define NGP_RENDER_THREADS 512
+#endif
+constexpr int kRenderThreads = NGP_RENDER_THREADS;   // whole warpgroups
 constexpr int kRenderWarps = kRenderThreads / 32;
+constexpr int kRenderGroups = kRenderWarps / 4;
+constexpr uint32_t kRenderTmemCols = kRenderGroups * 64 <= 256 ? 256 : 512;   // power of two >= 64 per warpgroup
+static_assert(kRenderThreads % 128 == 0 && kRenderGroups <= 8, "the renderer is built from warpgroups; TMEM holds 8 tiles");
 constexpr int kMaxStep = 8;                    // renderer.py:357
 constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
 constexpr int kMaxSamplesPerEpoch = 128;      // E * s cap: bounds the longest tile of an epoch
@@ -352,12 +359,6 @@ struct RenderCtr {
     unsigned long long samples;
     uint32_t error;
 };
-
-struct WarpSmem {
-    __half enc[32 * kEncStride];               // A-operand staging of the current 32 rows; first 16 B of a row = (sigma, r, g, b) after the MLPs
-    __half sh[32 * kShStride];                 // degree-4 SH of lane r's ray direction
-};
-static_assert(sizeof(WarpSmem) % 16 == 0 && offsetof(WarpSmem, sh) % 16 == 0, "WarpSmem alignment");
 
 struct RenderArgs {
     const float *rays_o, *rays_d;
@@ -464,48 +465,59 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
     }
 }
 
-// EVALUATE + COMPOSITE phase of one epoch for one warp (see the header comment).
+// EVALUATE + COMPOSITE phase of one epoch for one WARPGROUP (see the header comment).  The four warps of a group each own a
+// 32-row sub-tile (their own R rays) exactly as before, but walk their passes in lockstep so that the 128 rows go through the
+// MLPs as ONE tcgen05 tile (tc_mlp.cuh): thread = row = TMEM lane.
+struct GroupSmem {
+    uint32_t ticket[2];   // the group's current / next tile (claimed one tile ahead)
+    uint32_t max_ne[4];   // per-warp pass counts of the current tile
+    uint32_t pad[2];
+};
+
 template <bool kProf>
-__device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs &ra, const uint2 *__restrict__ s_w, WarpSmem &ws, int lane,
+__device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs &ra, tc::Tile &tt, GroupSmem &gs, __half *s_sh, int lane, int wg_tid,
                                            uint32_t lt_mask, const int *__restrict__ alive_in, int *__restrict__ alive_out,
                                            const float4 *__restrict__ state_in, float4 *__restrict__ state_out, uint32_t n_alive,
                                            uint32_t s, uint32_t ES, const TileGeom tg, uint32_t seq, EpochCtr *ec, uint32_t *s_hist,
                                            long long (&pc)[8]) {
     const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
-    const uint32_t n_tiles = (n_alive + R - 1) / R;
+    const uint32_t n_tiles = (n_alive + R - 1) / R;          // 32-row warp tiles
+    const uint32_t n_gtiles = (n_tiles + 3) / 4;             // 128-row group tiles
     const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
     const bool leader = my_k == 0;
     const int lead_lane = lane & ~(int)(K - 1u);
+    const int wwarp = wg_tid >> 5;                           // warp within the group
     const size_t tile_rows = (size_t)R * tg.ESp;
+    float4 *scratch = reinterpret_cast<float4 *>(tt.a + 4 * tc::kRows) + 2 * wg_tid;   // this row's 32 B in the idle half of the A tile
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
-    uint32_t next_tile = 0;
-    if (lane == 0) next_tile = atomicAdd(&ec->ticket, 1u);
-    next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
+    uint32_t par = 0;
+    if (wg_tid == 0) gs.ticket[0] = atomicAdd(&ec->ticket, 1u);
+    tc::group_sync(tt.bar_id);
+    uint32_t gtile = gs.ticket[0];
     int nx_index = 0;
     uint32_t nx_ne = 0;
-    if (next_tile < n_tiles && next_tile * R + my_r < n_alive) {
-        nx_index = __ldcg(alive_in + next_tile * R + my_r);
-        nx_ne = __ldcg(ra.n_emit + next_tile * R + my_r);
+    if (gtile < n_gtiles) {
+        const uint32_t n = (gtile * 4 + wwarp) * R + my_r;
+        if (n < n_alive) { nx_index = __ldcg(alive_in + n); nx_ne = __ldcg(ra.n_emit + n); }
     }
-    for (;;) {
-        const uint32_t tile = next_tile;
-        if (tile >= n_tiles) break;
-        const bool has_ray = tile * R + my_r < n_alive;
+    while (gtile < n_gtiles) {
+        const uint32_t tile = gtile * 4 + wwarp;
+        const bool has_ray = tile * R + my_r < n_alive;      // false for the whole warp if the group tile is ragged
         const int index = nx_index;
-        const uint32_t ne = has_ray ? min(nx_ne, ES) : 0u;       // ES may be shorter than what was marched (pre-validated epoch)
-        if (lane == 0) next_tile = atomicAdd(&ec->ticket, 1u);   // claimed now, read after the first pass: its latency is hidden
-        bool fetched_next = false;
+        const uint32_t ne = has_ray ? min(nx_ne, ES) : 0u;   // ES may be shorter than what was marched (pre-validated epoch)
+        uint32_t next_ticket = 0;
+        if (wg_tid == 0) next_ticket = atomicAdd(&ec->ticket, 1u);   // claimed now, published after the passes: its latency is hidden
         const size_t tbase = (size_t)tile * tile_rows + lane;
         float4 sa = make_float4(0.f, 0.f, 0.f, 0.f);
         float sb = 0.f;
         if (my_k < ne) { sa = __ldcs(ra.smp_a + tbase); sb = __ldcs(ra.smp_b + tbase); }
         RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         uint32_t samples = 0;
+        uint4 *srow = reinterpret_cast<uint4 *>(s_sh + my_r * 16);
         if (has_ray && leader) {
             const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
             const float *d = ra.rays_d + (size_t)index * 3;
-            uint4 *srow = reinterpret_cast<uint4 *>(ws.sh + my_r * kShStride);
             sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), srow[0], srow[1]);   // the direction is constant along the ray
             a.t = r0.x; a.ws = r0.y; a.d = r0.z; a.r = r1.x; a.g = r1.y; a.b = r1.z;
             samples = __float_as_uint(r1.w);
@@ -513,6 +525,9 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
         uint32_t max_ne = ne;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) max_ne = max(max_ne, __shfl_xor_sync(0xffffffffu, max_ne, o));
+        if (lane == 0) gs.max_ne[wwarp] = max_ne;
+        tc::group_sync(tt.bar_id);                           // also orders the SH rows before their first read
+        max_ne = max(max(gs.max_ne[0], gs.max_ne[1]), max(gs.max_ne[2], gs.max_ne[3]));
         bool dead = false;           // the ray of this lane (leader decides, group follows)
         uint32_t death = 0;          // leader: iteration of the epoch this ray died in
         uint32_t chunk = 0, in_chunk = 0;   // leader: position of the next sample in the reference's chunking
@@ -520,57 +535,53 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
         for (uint32_t i0 = 0; i0 < max_ne; i0 += K) {
             const uint32_t i = i0 + my_k;
             const bool active = !dead && i < ne;
-            if (!__any_sync(0xffffffffu, active)) break;
+            uint32_t any;
+            asm volatile(
+                "{\n\t"
+                ".reg .pred p, q;\n\t"
+                "setp.ne.b32 q, %1, 0;\n\t"
+                "bar.red.or.pred p, %2, 128, q;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t"
+                "}\n"
+                : "=r"(any)
+                : "r"((uint32_t)active), "r"(tt.bar_id)
+                : "memory");
+            if (!any) break;
             const float4 ca = sa;
             const float cb = sb;
             if (!dead && i + K < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i0 + K) * R); sb = __ldcs(ra.smp_b + tbase + (size_t)(i0 + K) * R); }
-            if (active) {
-                encode_point(nc, ca.x, ca.y, ca.z, reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride));
-                *reinterpret_cast<float2 *>(ws.enc + lane * kEncStride + 32) = make_float2(ca.w, cb);   // (dt, delta_t) in the row's pad
-            }
-            __syncwarp();
+            if (active) encode_point(nc, ca.x, ca.y, ca.z, tt.a + wg_tid, tc::kRows);
             NGP_PROF(3)
-            mlp_rows32(nc, s_w, ws.enc, [&](int rr) { return ws.sh + ((uint32_t)rr >> kshift) * kShStride; }, 0, lane,
-                       [&](int rr, float sg) { reinterpret_cast<float *>(ws.enc + rr * kEncStride)[0] = sg; },
-                       [&](int rr, int t, float v0, float v1) {
-                           float *o = reinterpret_cast<float *>(ws.enc + rr * kEncStride);
-                           if (t == 0) { o[1] = v0; o[2] = v1; } else { o[3] = v0; }
-                       });
-            __syncwarp();
-            if (leader && has_ray && !dead) {   // composite this pass's <= K samples of the ray in order (raymarching.cu:866-894)
-                const uint32_t cnt = min(K, ne - min(ne, i0));
-                for (uint32_t k = 0; k < cnt; k++) {
-                    const __half *row = ws.enc + (lane + k) * kEncStride;
-                    const float4 o = *reinterpret_cast<const float4 *>(row);
-                    const float2 dd = *reinterpret_cast<const float2 *>(row + 32);
-                    const bool term = composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y);
-                    if (term) {
-                        dead = true;
-                        death = chunk;
-                        samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
-                        break;
+            float sg, cr, cg, cbl;
+            const uint4 sh_lo = srow[0], sh_hi = srow[1];
+            tc::mlp_tile128(tt, wg_tid, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, cr, cg, cbl);
+            if (K == 1) {
+                if (active && composite_sample(a, sg, cr, cg, cbl, ca.w, cb)) {   // raymarching.cu:866-894
+                    dead = true;
+                    death = chunk;
+                    samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
+                }
+                if (++in_chunk == s) { in_chunk = 0; chunk++; }
+            } else {
+                scratch[0] = make_float4(sg, cr, cg, cbl);
+                scratch[1] = make_float4(ca.w, cb, 0.f, 0.f);
+                __syncwarp();
+                if (leader && has_ray && !dead) {   // composite this pass's <= K samples of the ray in order
+                    const uint32_t cnt = min(K, ne - min(ne, i0));
+                    for (uint32_t k = 0; k < cnt; k++) {
+                        const float4 o = scratch[2 * k], dd = scratch[2 * k + 1];
+                        if (composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y)) {
+                            dead = true;
+                            death = chunk;
+                            samples += min(ne, (chunk + 1) * s);
+                            break;
+                        }
+                        if (++in_chunk == s) { in_chunk = 0; chunk++; }
                     }
-                    if (++in_chunk == s) { in_chunk = 0; chunk++; }
                 }
+                dead = __shfl_sync(0xffffffffu, dead, lead_lane);
             }
-            if (K > 1) dead = __shfl_sync(0xffffffffu, dead, lead_lane);
-            if (!fetched_next) {   // the next tile's list entries, one tile ahead of their use
-                fetched_next = true;
-                next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
-                if (next_tile < n_tiles && next_tile * R + my_r < n_alive) {
-                    nx_index = __ldcg(alive_in + next_tile * R + my_r);
-                    nx_ne = __ldcg(ra.n_emit + next_tile * R + my_r);
-                }
-            }
-            __syncwarp();
             NGP_PROF(4)
-        }
-        if (!fetched_next) {
-            next_tile = __shfl_sync(0xffffffffu, next_tile, 0);
-            if (next_tile < n_tiles && next_tile * R + my_r < n_alive) {
-                nx_index = __ldcg(alive_in + next_tile * R + my_r);
-                nx_ne = __ldcg(ra.n_emit + next_tile * R + my_r);
-            }
         }
         // ---- end of the epoch for these rays: who survives (raymarching.cu:896-911), tentative state, next live list
         bool survives = false;
@@ -592,7 +603,15 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
             base = __shfl_sync(0xffffffffu, base, 0);
             if (survives) __stcg(alive_out + base + __popc(ballot & lt_mask), index);
         }
-        __syncwarp();   // ws is rewritten by the next tile
+        // ---- next group tile
+        par ^= 1u;
+        if (wg_tid == 0) gs.ticket[par] = next_ticket;
+        tc::group_sync(tt.bar_id);   // publishes the ticket; also: everyone is done with this tile's SH rows and scratch
+        gtile = gs.ticket[par];
+        if (gtile < n_gtiles) {
+            const uint32_t n = (gtile * 4 + wwarp) * R + my_r;
+            if (n < n_alive) { nx_index = __ldcg(alive_in + n); nx_ne = __ldcg(ra.n_emit + n); }
+        }
         NGP_PROF(5)
     }
 #undef NGP_PROF
@@ -601,20 +620,44 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
 template <bool kProf>
 __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, RenderArgs ra) {
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch];
-    uint2 *s_w = reinterpret_cast<uint2 *>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    WarpSmem &ws = reinterpret_cast<WarpSmem *>(s_w + nc.wpack_count)[warp];
-    uint32_t *s_coarse = ra.coarse ? reinterpret_cast<uint32_t *>(reinterpret_cast<WarpSmem *>(s_w + nc.wpack_count) + kRenderWarps) : nullptr;
+    __shared__ __align__(8) uint64_t s_mbar[kRenderGroups];
+    __shared__ GroupSmem s_group[kRenderGroups];
+    __shared__ uint32_t s_tmem;
+    // dynamic shared memory: [tcgen05 weights][A tiles, 16 KB per warpgroup][SH rows, 1 KB per warp][coarse occupancy]
+    uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
+    uint4 *s_a = s_w + nc.wtc_bytes / 16;
+    __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * 8 * tc::kRows);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, wg = warp >> 2, wg_tid = tid & 127;
+    uint32_t *s_coarse = ra.coarse ? reinterpret_cast<uint32_t *>(s_sh_all + (size_t)kRenderWarps * 32 * 16) : nullptr;
     const uint32_t N = ra.N;
     const uint32_t lt_mask = (1u << lane) - 1u;
     long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const long long k_start = kProf ? clock64() : 0;
-    copy_wpack_to_smem(nc, s_w);
+    for (uint32_t i = tid; i < nc.wtc_bytes / 16; i += blockDim.x) s_w[i] = __ldg(nc.wtc + i);
+    tc::fence_async_smem();
     if (s_coarse)
         for (uint32_t i = tid; i < ra.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(ra.coarse + i);
     if (tid < kMaxEpoch) s_hist[tid] = 0;
+    if (warp == 0) tc::tmem_alloc(tc::smem_u32(&s_tmem), kRenderTmemCols);
+    if (tid == 0) {
+        for (int g = 0; g < kRenderGroups; g++) tc::mbar_init(tc::smem_u32(&s_mbar[g]), 1);
+        tc::mbar_init_fence();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(&s_tmem);
+    tc::Tile tt;
+    tt.a = s_a + (size_t)wg * 8 * tc::kRows;
+    tt.a_saddr = tc::smem_u32(tt.a);
+    tt.w_saddr = tc::smem_u32(s_w);
+    tt.mbar_saddr = tc::smem_u32(&s_mbar[wg]);
+    tt.tmem = tmem_base + (uint32_t)wg * tc::kTmemColsPerTile + ((uint32_t)((warp & 3) * 32) << 16);
+    tt.bar_id = 1u + (uint32_t)wg;
+    tt.parity = 0;
+    __half *s_sh = s_sh_all + (size_t)warp * 32 * 16;
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
@@ -698,7 +741,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         }
         __syncthreads();   // s_val is rewritten below
         if (kProf) pc[2] += clock64() - g0;
-        eval_phase<kProf>(nc, ra, s_w, ws, lane, lt_mask, alive_in, alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, pc);
+        eval_phase<kProf>(nc, ra, tt, s_group[wg], s_sh, lane, wg_tid, lt_mask, alive_in, alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, pc);
         if (kProf) g0 = clock64();
         __syncthreads();
         if (tid < kMaxEpoch) {
@@ -775,6 +818,9 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             ra.stats[3] = (long long)replays;
         }
     }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem_base, kRenderTmemCols);
 }
 
 }  // namespace ngp
@@ -813,7 +859,7 @@ struct ngp_ctx {
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + (size_t)kRenderWarps * sizeof(WarpSmem); }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * 8 * tc::kRows * 16 + (size_t)kRenderWarps * 32 * 32; }
 
 extern "C" {
 
@@ -867,6 +913,7 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
     for (uint32_t l = 0; l < L; l++) {
         LevelConst &lc = nc.lv[l];
         lc.offset = (uint32_t)offsets_host[l];
+        nc.lvbase[l] = nc.table + lc.offset;
         lc.size = (uint32_t)(offsets_host[l + 1] - offsets_host[l]);
         lc.scale = h_scales[l];
         const uint32_t res = (uint32_t)ceilf(lc.scale) + 1;

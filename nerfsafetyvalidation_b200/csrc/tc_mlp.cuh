@@ -166,9 +166,10 @@ __device__ __forceinline__ void layer_mma(Tile &t, int row, uint32_t w_off, uint
             mma_f16_ss(tmem_d, ad, bd, idesc, k > 0 ? 1u : 0u);
         }
         mma_commit(t.mbar_saddr);
+        mbar_wait(t.mbar_saddr, t.parity);   // one poller per warpgroup; the other 127 threads sleep in the hardware barrier below
     }
-    mbar_wait(t.mbar_saddr, t.parity);
     t.parity ^= 1u;
+    group_sync(t.bar_id);
     fence_after_sync();
 }
 

@@ -80,8 +80,10 @@ class NeRFNetwork(NeRFRenderer):
             M = x.shape[0]
             sig = torch.empty(M, dtype=torch.float32, device=x.device)
             rgb = torch.empty(M, 3, dtype=torch.float32, device=x.device)
-            _cabi.check(lib.ngp_network_forward(self._native.get(), _cabi.ptr(x), _cabi.ptr(d), M, 0, _cabi.ptr(sig), _cabi.ptr(rgb),
-                                                _cabi.stream()), "ngp_network_forward")
+            # both MLPs on tcgen05 (128-row tiles, TMEM accumulators) unless the mma.sync formulation is asked for; same results
+            fn = lib.ngp_network_forward if getattr(self, "mlp_engine", "tcgen05") == "mma_sync" else lib.ngp_network_forward_tc
+            _cabi.check(fn(self._native.get(), _cabi.ptr(x), _cabi.ptr(d), M, 0, _cabi.ptr(sig), _cabi.ptr(rgb), _cabi.stream()),
+                        "ngp_network_forward")
             return sig, rgb
         return self._forward_unfused(x, d)
 

@@ -311,6 +311,19 @@ def test_network_forward(frame, cuda, variant):
         sig, rgb = ours(x, d)
         sig_u, rgb_u = ours._forward_unfused(x, d)
     assert sig.shape == (20000,) and rgb.shape == (20000, 3)
+    # the default engine is tcgen05 (TMEM accumulators); the mma.sync formulation of the same MLPs must agree bit for bit: both
+    # accumulate each layer in fp32 over K in the same 16-wide steps and round to fp16 at the same points
+    ours.mlp_engine = "mma_sync"
+    try:
+        with torch.no_grad():
+            sig_m, rgb_m = ours(x, d)
+    finally:
+        ours.mlp_engine = "tcgen05"
+    assert ((sig - sig_m).abs() / sig_m.abs().clamp_min(1e-6)).max().item() <= 1e-6 and (rgb - rgb_m).abs().max().item() <= 1e-6
+    for M in (1, 127, 129):   # ragged tiles
+        with torch.no_grad():
+            s1, c1 = ours(x[:M], d[:M])
+        assert torch.equal(s1, sig[:M]) and torch.equal(c1, rgb[:M])
     lib = _cabi.load()
     scales = torch.empty(16, dtype=torch.float32, device=cuda)
     _cabi.check(lib.ngp_grid_level_scales(16, w["S"], 16, _cabi.ptr(scales), _cabi.stream()))

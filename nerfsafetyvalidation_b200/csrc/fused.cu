@@ -47,54 +47,62 @@ __device__ __forceinline__ void copy_wpack_to_smem(const NetConst &nc, uint2 *s_
     for (uint32_t i = threadIdx.x; i < nc.wpack_count / 2; i += blockDim.x) dst[i] = __ldg(src + i);
 }
 
-// 16-level hash-grid encoding of one point into 16 half2 (= 4 x uint4) of shared memory.
-// dst[g * stride], g = 0..3, receives levels 4g .. 4g+3 (8 halves).
+// grid.py:144  inputs = (inputs + bound) / (2 * bound); returns false when the point lies outside [0,1]^3 (gridencoder.cu:99-123:
+// the encoding is all zeros then)
+__device__ __forceinline__ bool encode_unit(const NetConst &nc, float x, float y, float z, float &u0, float &u1, float &u2) {
+    u0 = __fdiv_rn(__fadd_rn(x, nc.bound), nc.two_bound);
+    u1 = __fdiv_rn(__fadd_rn(y, nc.bound), nc.two_bound);
+    u2 = __fdiv_rn(__fadd_rn(z, nc.bound), nc.two_bound);
+    return !((u0 < 0 || u0 > 1) || (u1 < 0 || u1 > 1) || (u2 < 0 || u2 > 1));
+}
+
+// One trip of the gather: levels 4 grp .. 4 grp + 3 of the point (u0, u1, u2) -> 8 halves.  32 independent 4-byte loads in flight.
+__device__ __forceinline__ uint4 encode_trip(const NetConst &nc, float u0, float u1, float u2, int grp) {
+    float f[4][3];
+    __half2 v[4][8];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const LevelConst &lc = nc.lv[grp * 4 + j];
+        const float scale = lc.scale;
+        float p0 = __fmaf_rn(u0, scale, 0.5f), p1 = __fmaf_rn(u1, scale, 0.5f), p2 = __fmaf_rn(u2, scale, 0.5f);
+        const uint32_t g0 = (uint32_t)floorf(p0), g1 = (uint32_t)floorf(p1), g2 = (uint32_t)floorf(p2);
+        f[j][0] = __fsub_rn(p0, (float)g0); f[j][1] = __fsub_rn(p1, (float)g1); f[j][2] = __fsub_rn(p2, (float)g2);
+        const __half2 *tl = nc.lvbase[grp * 4 + j];
+        uint32_t row[8];
+        cell_rows(lc, g0, g1, g2, row);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
+    }
+    uint32_t packed[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
+        const float q0 = 1.0f - p0, q1 = 1.0f - p1, q2 = 1.0f - p2;
+        const float w00 = q0 * q1, w10 = p0 * q1, w01 = q0 * p1, w11 = p0 * p1;   // (w_x * w_y) * w_z, gridencoder.cu:148-160
+        const float w[8] = {w00 * q2, w10 * q2, w01 * q2, w11 * q2, w00 * p2, w10 * p2, w01 * p2, w11 * p2};
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const float2 g = __half22float2(v[j][k]);
+            a0 = fmaf(w[k], g.x, a0);
+            a1 = fmaf(w[k], g.y, a1);
+        }
+        packed[j] = pack_half2(a0, a1);
+    }
+    return make_uint4(packed[0], packed[1], packed[2], packed[3]);
+}
+
+// 16-level hash-grid encoding of one point into 16 half2: dst[g * stride], g = 0..3, receives levels 4g .. 4g+3 (8 halves).
 __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float y, float z, uint4 *dst, int stride = 1) {
-    // grid.py:144  inputs = (inputs + bound) / (2 * bound)
-    const float u0 = __fdiv_rn(__fadd_rn(x, nc.bound), nc.two_bound);
-    const float u1 = __fdiv_rn(__fadd_rn(y, nc.bound), nc.two_bound);
-    const float u2 = __fdiv_rn(__fadd_rn(z, nc.bound), nc.two_bound);
-    if ((u0 < 0 || u0 > 1) || (u1 < 0 || u1 > 1) || (u2 < 0 || u2 > 1)) {  // gridencoder.cu:99-123
+    float u0, u1, u2;
+    if (!encode_unit(nc, x, y, z, u0, u1, u2)) {
         dst[0] = dst[stride] = dst[2 * stride] = dst[3 * stride] = make_uint4(0, 0, 0, 0);
         return;
     }
-    // 4 levels (32 independent 4-byte gathers) per trip; the trip loop is deliberately NOT unrolled: the renderer's 16 warps
-    // sit in different phases, and a 4x smaller gather body keeps them inside the instruction cache
+    // the trip loop is deliberately NOT unrolled: a 4x smaller gather body keeps the renderer's warps, which sit in different
+    // phases, inside the instruction cache
 #pragma unroll 1
-    for (int grp = 0; grp < 4; grp++) {
-        float f[4][3];
-        __half2 v[4][8];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const LevelConst &lc = nc.lv[grp * 4 + j];
-            const float scale = lc.scale;
-            float p0 = __fmaf_rn(u0, scale, 0.5f), p1 = __fmaf_rn(u1, scale, 0.5f), p2 = __fmaf_rn(u2, scale, 0.5f);
-            const uint32_t g0 = (uint32_t)floorf(p0), g1 = (uint32_t)floorf(p1), g2 = (uint32_t)floorf(p2);
-            f[j][0] = __fsub_rn(p0, (float)g0); f[j][1] = __fsub_rn(p1, (float)g1); f[j][2] = __fsub_rn(p2, (float)g2);
-            const __half2 *tl = nc.lvbase[grp * 4 + j];
-            uint32_t row[8];
-            cell_rows(lc, g0, g1, g2, row);
-#pragma unroll
-            for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
-        }
-        uint32_t packed[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
-            const float q0 = 1.0f - p0, q1 = 1.0f - p1, q2 = 1.0f - p2;
-            const float w00 = q0 * q1, w10 = p0 * q1, w01 = q0 * p1, w11 = p0 * p1;   // (w_x * w_y) * w_z, gridencoder.cu:148-160
-            const float w[8] = {w00 * q2, w10 * q2, w01 * q2, w11 * q2, w00 * p2, w10 * p2, w01 * p2, w11 * p2};
-            float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const float2 g = __half22float2(v[j][k]);
-                a0 = fmaf(w[k], g.x, a0);
-                a1 = fmaf(w[k], g.y, a1);
-            }
-            packed[j] = pack_half2(a0, a1);
-        }
-        dst[grp * stride] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-    }
+    for (int grp = 0; grp < 4; grp++) dst[grp * stride] = encode_trip(nc, u0, u1, u2, grp);
 }
 
 // degree-4 SH of a direction -> 16 halves (2 x uint4)
@@ -283,6 +291,7 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
     tc::Tile t;
     t.a = s_a; t.a_saddr = tc::smem_u32(s_a); t.w_saddr = tc::smem_u32(s_w); t.mbar_saddr = tc::smem_u32(s_mbar);
     t.tmem = tmem_base + ((uint32_t)(warp * 32) << 16); t.bar_id = 1; t.parity = 0;
+    t.e = s_a; t.e_saddr = t.a_saddr; t.aready_saddr = 0; t.parity_a = 0;
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint32_t row = tile * tc::kRows + tid;
         uint4 sh_lo = make_uint4(0, 0, 0, 0), sh_hi = sh_lo;
@@ -531,6 +540,7 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
         bool dead = false;           // the ray of this lane (leader decides, group follows)
         uint32_t death = 0;          // leader: iteration of the epoch this ray died in
         uint32_t chunk = 0, in_chunk = 0;   // leader: position of the next sample in the reference's chunking
+        uint4 *const erow = tt.e + wg_tid;
         NGP_PROF(0)
         for (uint32_t i0 = 0; i0 < max_ne; i0 += K) {
             const uint32_t i = i0 + my_k;
@@ -547,14 +557,14 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
                 : "r"((uint32_t)active), "r"(tt.bar_id)
                 : "memory");
             if (!any) break;
+            float sg, cr, cg, cbl;
+            const uint4 sh_lo = srow[0], sh_hi = srow[1];
             const float4 ca = sa;
             const float cb = sb;
             if (!dead && i + K < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i0 + K) * R); sb = __ldcs(ra.smp_b + tbase + (size_t)(i0 + K) * R); }
-            if (active) encode_point(nc, ca.x, ca.y, ca.z, tt.a + wg_tid, tc::kRows);
+            if (active) encode_point(nc, ca.x, ca.y, ca.z, erow, tc::kRows);
             NGP_PROF(3)
-            float sg, cr, cg, cbl;
-            const uint4 sh_lo = srow[0], sh_hi = srow[1];
-            tc::mlp_tile128(tt, wg_tid, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, cr, cg, cbl);
+            tc::mlp_tile128_pipelined(tt, wg_tid, lane, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, cr, cg, cbl, [](int) {});
             if (K == 1) {
                 if (active && composite_sample(a, sg, cr, cg, cbl, ca.w, cb)) {   // raymarching.cu:866-894
                     dead = true;
@@ -621,14 +631,14 @@ template <bool kProf>
 __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, RenderArgs ra) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch];
-    __shared__ __align__(8) uint64_t s_mbar[kRenderGroups];
+    __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch], s_mval[kMaxEpoch];
+    __shared__ __align__(8) uint64_t s_mbar[kRenderGroups], s_aready[kRenderGroups];
     __shared__ GroupSmem s_group[kRenderGroups];
     __shared__ uint32_t s_tmem;
     // dynamic shared memory: [tcgen05 weights][A tiles, 16 KB per warpgroup][SH rows, 1 KB per warp][coarse occupancy]
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
     uint4 *s_a = s_w + nc.wtc_bytes / 16;
-    __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * 8 * tc::kRows);
+    __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * 12 * tc::kRows);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, wg = warp >> 2, wg_tid = tid & 127;
     uint32_t *s_coarse = ra.coarse ? reinterpret_cast<uint32_t *>(s_sh_all + (size_t)kRenderWarps * 32 * 16) : nullptr;
     const uint32_t N = ra.N;
@@ -642,7 +652,10 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     if (tid < kMaxEpoch) s_hist[tid] = 0;
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(&s_tmem), kRenderTmemCols);
     if (tid == 0) {
-        for (int g = 0; g < kRenderGroups; g++) tc::mbar_init(tc::smem_u32(&s_mbar[g]), 1);
+        for (int g = 0; g < kRenderGroups; g++) {
+            tc::mbar_init(tc::smem_u32(&s_mbar[g]), 1);
+            tc::mbar_init(tc::smem_u32(&s_aready[g]), 4);   // one arrival per warp of the group
+        }
         tc::mbar_init_fence();
     }
     tc::fence_before_sync();
@@ -650,8 +663,12 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     tc::fence_after_sync();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(&s_tmem);
     tc::Tile tt;
-    tt.a = s_a + (size_t)wg * 8 * tc::kRows;
+    tt.a = s_a + (size_t)wg * 12 * tc::kRows;      // 8 chunks of hidden activations + 4 chunks of encoding staging
     tt.a_saddr = tc::smem_u32(tt.a);
+    tt.e = tt.a + 8 * tc::kRows;
+    tt.e_saddr = tc::smem_u32(tt.e);
+    tt.aready_saddr = tc::smem_u32(&s_aready[wg]);
+    tt.parity_a = 0;
     tt.w_saddr = tc::smem_u32(s_w);
     tt.mbar_saddr = tc::smem_u32(&s_mbar[wg]);
     tt.tmem = tmem_base + (uint32_t)wg * tc::kTmemColsPerTile + ((uint32_t)((warp & 3) * 32) << 16);
@@ -673,7 +690,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     }
     grid.sync();
 
-    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = N, E = 1, replays = 0;
+    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = N, E = 1, replays = 0, t_deaths = 0;
     bool replay = false;
     while (step < ra.max_steps && n_alive > 0) {
         const uint32_t s = clamp_n_step(N, n_alive);                         // renderer.py:357
@@ -682,7 +699,9 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             else {
                 const uint32_t margin = n_alive - N / (s + 1);               // deaths until N // n_alive reaches s + 1
                 const uint32_t rate = last_rate < 1u ? 1u : last_rate;
-                const uint32_t e = margin / (2u * rate);
+                // pre-validation makes over-shooting cheap (only marching is wasted) as long as rays die by running out of samples;
+                // transmittance deaths are only found by the evaluator, so be conservative once they show up
+                const uint32_t e = t_deaths ? margin / (2u * rate) : (margin + margin / 2u) / rate + 1u;
                 E = e < 1u ? 1u : (e > (uint32_t)kMaxEpoch ? (uint32_t)kMaxEpoch : e);
             }
             if (ra.max_epoch && E > ra.max_epoch) E = ra.max_epoch;
@@ -727,7 +746,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         grid.sync();
         // ---- pre-validation: the rays that ran out of samples are known now.  If they alone move n_step at iteration j, only
         //      the first j iterations of what was marched are evaluated (the marched samples of those are exact).
-        if (tid < kMaxEpoch) s_val[tid] = tid < (int)E ? __ldcg(&ec->mhist[tid]) : 0u;
+        if (tid < kMaxEpoch) s_val[tid] = s_mval[tid] = tid < (int)E ? __ldcg(&ec->mhist[tid]) : 0u;
         __syncthreads();
         {
             uint32_t na = n_alive, ok_iters = 0;
@@ -754,7 +773,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         __syncthreads();
         // ---- validate the speculation: replay the reference's schedule over the epoch's death histogram
         uint32_t na = n_alive, ran = 0, last = 0;
-        bool ok = true;
+        bool ok = true, any_t = false;
         for (uint32_t j = 0; j < E; j++) {
             if (j > 0) {
                 if (na == 0) break;                                         // renderer.py:352-353: the loop ended here
@@ -763,6 +782,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             last = s_val[j];
             na -= last;
             ran++;
+            if (last != s_mval[j]) any_t = true;   // somebody died here without running out of samples: transmittance
         }
         __syncthreads();   // s_val is rewritten after the next epoch
         if (kProf) pc[6] += clock64() - g0;
@@ -778,6 +798,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         step += ran * s;
         iter += ran;
         last_rate = last;
+        t_deaths = any_t ? 1u : 0u;
         n_alive = na;
         in ^= 1;
     }
@@ -859,7 +880,7 @@ struct ngp_ctx {
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * 8 * tc::kRows * 16 + (size_t)kRenderWarps * 32 * 32; }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * 12 * tc::kRows * 16 + (size_t)kRenderWarps * 32 * 32; }
 
 extern "C" {
 
@@ -1095,7 +1116,8 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     }
     NetConst nc = c->nc;
     void *args[] = {&nc, &ra};
-    NGP_CUDA(cudaLaunchCooperativeKernel(c->prof ? (const void *)k_render<true> : (const void *)k_render<false>, dim3(c->render_blocks), dim3(kRenderThreads), args, smem, st));
+    const void *fn = c->prof ? (const void *)k_render<true> : (const void *)k_render<false>;
+    NGP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(c->render_blocks), dim3(kRenderThreads), args, smem, st));
     return after_launch("render");
 }
 

@@ -55,6 +55,9 @@ __device__ __forceinline__ void group_sync(uint32_t bar_id) { asm volatile("bar.
 __device__ __forceinline__ void mbar_init(uint32_t mbar_saddr, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar_saddr), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t mbar_saddr) {   // release at CTA scope
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mbar_saddr) : "memory");
+}
 __device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void mbar_wait(uint32_t mbar_saddr, uint32_t parity) {
     uint32_t done = 0, spins = 0;
@@ -148,6 +151,11 @@ struct Tile {
     uint32_t tmem;        // TMEM address of this tile's 64 accumulator columns, lane field = this WARP's first lane
     uint32_t bar_id;      // named barrier of this warpgroup (1..15)
     uint32_t parity;      // phase of the mbarrier
+    // pipelined variant only (mlp_tile128_pipelined)
+    uint4 *e;             // encoding staging: uint4 [4][128] (8 KB), the first layer's A operand
+    uint32_t e_saddr;
+    uint32_t aready_saddr;   // mbarrier (count 4): every warp of the group has stored its rows of the next A operand
+    uint32_t parity_a;
 };
 
 // One layer: D[128 x N] (TMEM) = A[128 x K] (smem) * W[N x K]^T (smem).  All 128 threads of the warpgroup call it after having
@@ -224,6 +232,78 @@ __device__ __forceinline__ void mlp_tile128(Tile &t, int row, uint32_t nh_sigma,
         r = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h0))));
         g = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h1))));
         b = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h2))));
+    }
+}
+
+// ---- pipelined variant: issue and completion of a layer are split, so that the caller can do independent work (the next pass's
+//      gather) while the tensor core runs and while the other warps of the group catch up.  No thread waits at a barrier:
+//        every warp     : stores its rows, fence.proxy.async, then ONE arrive on `aready` (count 4)
+//        thread 0       : waits for `aready`, issues the MMAs, commits to `mbar`
+//        every thread   : ... independent work ..., then waits for `mbar` (normally already complete)
+__device__ __forceinline__ void layer_issue(Tile &t, int row, int lane, uint32_t a_saddr, uint32_t w_off, uint32_t N, uint32_t K) {
+    fence_async_smem();      // this thread's A-row stores -> visible to the tensor core's (async proxy) reads
+    fence_before_sync();     // this thread's tcgen05.ld of the previous accumulators are ordered before the arrive
+    __syncwarp();
+    if (lane == 0) mbar_arrive(t.aready_saddr);
+    if (row == 0) {
+        mbar_wait(t.aready_saddr, t.parity_a);
+        fence_after_sync();
+        const uint32_t idesc = instr_desc(N);
+        const uint32_t tmem_d = t.tmem & 0x0000FFFFu;
+        for (uint32_t k = 0; k < K / 16; k++) {
+            const uint64_t ad = smem_desc(a_saddr + k * 2 * (kRows * 16), kRows * 16, 128);
+            const uint64_t bd = smem_desc(t.w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
+            mma_f16_ss(tmem_d, ad, bd, idesc, k > 0 ? 1u : 0u);
+        }
+        mma_commit(t.mbar_saddr);
+    }
+    t.parity_a ^= 1u;
+    __syncwarp();
+}
+__device__ __forceinline__ void layer_wait(Tile &t) {
+    mbar_wait(t.mbar_saddr, t.parity);
+    t.parity ^= 1u;
+    fence_after_sync();
+}
+
+// As mlp_tile128, with the first layer's A operand in t.e and `between(step)` called after the MMAs of layer `step` (0-based, in
+// evaluation order) have been handed to the tensor core.  `between` must not touch t.a, and may write t.e only for step >= 1.
+template <class Between>
+__device__ __forceinline__ void mlp_tile128_pipelined(Tile &t, int row, int lane, uint32_t nh_sigma, uint32_t nh_color, float density_scale,
+                                                      const uint4 &sh_lo, const uint4 &sh_hi, float &sigma, float &r, float &g, float &b,
+                                                      Between &&between) {
+    const WeightMap wm = weight_map(nh_sigma, nh_color);
+    const int n_sig = 2 + (int)nh_sigma, n_all = n_sig + 2 + (int)nh_color;
+    // one rolled loop over the layers of both nets: whatever `between` does (a gather trip) exists ONCE in the instruction stream
+#pragma unroll 1
+    for (int step = 0; step < n_all; step++) {
+        const bool in_color = step >= n_sig;
+        const int l = in_color ? step - n_sig : step;                           // layer within its net
+        const bool first = l == 0, last = l == (int)(in_color ? nh_color : nh_sigma) + 1;
+        const uint32_t w_off = (in_color ? wm.c0 : wm.s0) + (first ? 0u : 4096u + (uint32_t)(l - 1) * 8192u);   // [32->64] is 4 KB, [64->64] 8 KB
+        layer_issue(t, row, lane, step == 0 ? t.e_saddr : t.a_saddr, w_off, last ? 16u : 64u, first ? 32u : 64u);
+        between(step);
+        layer_wait(t);
+        if (!last) {
+            relu_row_to_a(t, row);
+        } else if (!in_color) {
+            float v[16];
+            tmem_ld16(t.tmem, v);
+            uint32_t g0 = pack_half2(v[0], v[1]);
+            sigma = expf(__half2float(__ushort_as_half((unsigned short)(g0 & 0xffffu)))) * density_scale;
+            g0 &= 0xffff0000u;   // column 0 (log-density) is not a colour feature
+            t.a[0 * kRows + row] = sh_lo;
+            t.a[1 * kRows + row] = sh_hi;
+            t.a[2 * kRows + row] = make_uint4(g0, pack_half2(v[2], v[3]), pack_half2(v[4], v[5]), pack_half2(v[6], v[7]));
+            t.a[3 * kRows + row] = make_uint4(pack_half2(v[8], v[9]), pack_half2(v[10], v[11]), pack_half2(v[12], v[13]), pack_half2(v[14], v[15]));
+        } else {
+            float v[4];
+            tmem_ld4(t.tmem, v);
+            const float h0 = __half2float(__float2half_rn(v[0])), h1 = __half2float(__float2half_rn(v[1])), h2 = __half2float(__float2half_rn(v[2]));
+            r = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h0))));
+            g = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h1))));
+            b = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h2))));
+        }
     }
 }
 

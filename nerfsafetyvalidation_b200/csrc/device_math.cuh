@@ -318,6 +318,20 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// Packed fp32 pairs (Blackwell FFMA2 / FMUL2: one issue slot for two IEEE round-to-nearest operations, results bit-identical to
+// two scalar instructions).
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long A = *reinterpret_cast<unsigned long long *>(&a), B = *reinterpret_cast<unsigned long long *>(&b),
+                       C = *reinterpret_cast<unsigned long long *>(&c), D;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(D) : "l"(A), "l"(B), "l"(C));
+    return *reinterpret_cast<float2 *>(&D);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+    unsigned long long A = *reinterpret_cast<unsigned long long *>(&a), B = *reinterpret_cast<unsigned long long *>(&b), D;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(D) : "l"(A), "l"(B));
+    return *reinterpret_cast<float2 *>(&D);
+}
+
 __device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
     const __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<const uint32_t *>(&h);

@@ -78,15 +78,18 @@ __device__ __forceinline__ uint4 encode_trip(const NetConst &nc, float u0, float
     for (int j = 0; j < 4; j++) {
         const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
         const float q0 = 1.0f - p0, q1 = 1.0f - p1, q2 = 1.0f - p2;
-        const float w00 = q0 * q1, w10 = p0 * q1, w01 = q0 * p1, w11 = p0 * p1;   // (w_x * w_y) * w_z, gridencoder.cu:148-160
-        const float w[8] = {w00 * q2, w10 * q2, w01 * q2, w11 * q2, w00 * p2, w10 * p2, w01 * p2, w11 * p2};
-        float a0 = 0.f, a1 = 0.f;
+        // (w_x * w_y) * w_z, gridencoder.cu:148-160, as packed pairs: (corner 2m, corner 2m + 1) differ in x only
+        const float2 wx = make_float2(q0, p0);
+        const float2 w0 = fmul2(wx, make_float2(q1, q1)), w1 = fmul2(wx, make_float2(p1, p1));
+        const float2 w[4] = {fmul2(w0, make_float2(q2, q2)), fmul2(w1, make_float2(q2, q2)), fmul2(w0, make_float2(p2, p2)),
+                             fmul2(w1, make_float2(p2, p2))};
+        float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const float2 g = __half22float2(v[j][k]);
-            a0 = fmaf(w[k], g.x, a0);
-            a1 = fmaf(w[k], g.y, a1);
+        for (int k = 0; k < 8; k++) {   // the reference's corner order; both channels in one FFMA2
+            const float wk = (k & 1) ? w[k >> 1].y : w[k >> 1].x;
+            acc = ffma2(make_float2(wk, wk), __half22float2(v[j][k]), acc);
         }
+        const float a0 = acc.x, a1 = acc.y;
         packed[j] = pack_half2(a0, a1);
     }
     return make_uint4(packed[0], packed[1], packed[2], packed[3]);
@@ -350,6 +353,15 @@ constexpr int kRenderWarps = kRenderThreads / 32;
 constexpr int kRenderGroups = kRenderWarps / 4;
 constexpr uint32_t kRenderTmemCols = kRenderGroups * 64 <= 256 ? 256 : 512;   // power of two >= 64 per warpgroup
 static_assert(kRenderThreads % 128 == 0 && kRenderGroups <= 8, "the renderer is built from warpgroups; TMEM holds 8 tiles");
+#ifndef NGP_TILE_CHUNKS
+#define NGP_TILE_CHUNKS 8
+#endif
+#ifndef NGP_EXTRA_SMEM
+#define NGP_EXTRA_SMEM 0
+#endif
+// 16-byte chunks of a warpgroup's A tile: 8 of hidden activations (+ 4 of encoding staging; with 8 the staging aliases the first
+// four activation chunks, which are idle between the last layer of one pass and the first epilogue of the next)
+constexpr int kTileChunks = NGP_TILE_CHUNKS;
 constexpr int kMaxStep = 8;                    // renderer.py:357
 constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
 constexpr int kMaxSamplesPerEpoch = 128;      // E * s cap: bounds the longest tile of an epoch
@@ -638,7 +650,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     // dynamic shared memory: [tcgen05 weights][A tiles, 16 KB per warpgroup][SH rows, 1 KB per warp][coarse occupancy]
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
     uint4 *s_a = s_w + nc.wtc_bytes / 16;
-    __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * 12 * tc::kRows);
+    __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * kTileChunks * tc::kRows);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, wg = warp >> 2, wg_tid = tid & 127;
     uint32_t *s_coarse = ra.coarse ? reinterpret_cast<uint32_t *>(s_sh_all + (size_t)kRenderWarps * 32 * 16) : nullptr;
     const uint32_t N = ra.N;
@@ -663,9 +675,9 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     tc::fence_after_sync();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(&s_tmem);
     tc::Tile tt;
-    tt.a = s_a + (size_t)wg * 12 * tc::kRows;      // 8 chunks of hidden activations + 4 chunks of encoding staging
+    tt.a = s_a + (size_t)wg * kTileChunks * tc::kRows;
     tt.a_saddr = tc::smem_u32(tt.a);
-    tt.e = tt.a + 8 * tc::kRows;
+    tt.e = kTileChunks >= 12 ? tt.a + 8 * tc::kRows : tt.a;
     tt.e_saddr = tc::smem_u32(tt.e);
     tt.aready_saddr = tc::smem_u32(&s_aready[wg]);
     tt.parity_a = 0;
@@ -880,7 +892,7 @@ struct ngp_ctx {
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * 12 * tc::kRows * 16 + (size_t)kRenderWarps * 32 * 32; }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * kTileChunks * tc::kRows * 16 + (size_t)kRenderWarps * 32 * 32 + NGP_EXTRA_SMEM; }
 
 extern "C" {
 

@@ -60,9 +60,14 @@ __device__ __forceinline__ void mbar_arrive(uint32_t mbar_saddr) {   // release 
 }
 __device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void mbar_wait(uint32_t mbar_saddr, uint32_t parity) {
-    uint32_t done = 0, spins = 0;
+    uint32_t done = 0;
+#ifdef NGP_SPIN_TRAP
+    uint32_t spins = 0;
+#endif
     do {
-        if (++spins == (1u << 28)) __trap();   // a tensor-core commit that never arrives must not hang the device
+#ifdef NGP_SPIN_TRAP   // development builds: a tensor-core commit that never arrives traps instead of hanging the device
+        if (++spins == (1u << 28)) __trap();
+#endif
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"

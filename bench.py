@@ -162,6 +162,33 @@ def cpu_port_mrays(wl, variant, n_rays, threads=None):
     return o.shape[0] / dt / 1e6, dt, o.shape[0], r
 
 
+def cpu_run_sampler_mrays(H=100, W=100):
+    """BASELINE.json configs[0] on the host cores: vanilla NeRF (frequency encoders, 11 264 params, torch.manual_seed(0) init)
+    rendering one 100x100 frame with the reference's pure-PyTorch `run()` sampler (64 + 64 samples, max_ray_batch 4096), restated
+    in oracle/run_sampler.py and pinned against the imported reference (tests/golden/pyref_cfg1.npz)."""
+    import math
+
+    import torch
+
+    from oracle import run_sampler as rs
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    fl = 0.5 * W / math.tan(0.5 * 0.6911112)
+    pose = np.eye(4, dtype=np.float32)
+    pose[2, 3] = -2.5
+    o, d = rs.get_rays(pose[None], fl, fl, W / 2, H / 2, H, W)
+    net = rs.VanillaNeRF(seed=0)
+    o, d = torch.from_numpy(o[0]), torch.from_numpy(d[0])
+    rs.render(net, o[:512], d[:512])   # warm-up (thread pool, allocator)
+    t0 = time.perf_counter()
+    out = rs.render(net, o, d, max_ray_batch=4096, num_steps=64, upsample_steps=64, bg_color=1.0)
+    dt = time.perf_counter() - t0
+    return {"value": H * W / dt / 1e6, "unit": "Mrays/s", "cores": cores, "seconds": dt, "kind": "port",
+            "what": f"cfg1: vanilla NeRF (frequency encoder, cuda_ray=False, 64+64 samples) rendering one {H}x{W} frame, "
+                    "oracle/run_sampler.py = the reference's NeRFRenderer.run restated in torch fp32 on CPU",
+            "mean_weights_sum": float(out["weights_sum"].mean())}
+
+
 def run_reference_arm(args, wl):
     """--impl reference: the CPU port of the reference path on all host threads, same metric / unit / config."""
     rank = int(os.environ.get("RANK", "0"))
@@ -185,6 +212,10 @@ def run_reference_arm(args, wl):
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port",
                              "sample": f"{rays} rays (every {max(1, wl['H'] * wl['W'] // n)}th ray of the frame) per step, oracle/ngp_oracle.c with OpenMP"},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    try:
+        line["cpu_reference_run"] = cpu_run_sampler_mrays()
+    except Exception as e:   # reported beside the arm, never instead of it
+        line["cpu_reference_run"] = {"unavailable": f"{type(e).__name__}: {e}"}
     print(json.dumps(line))
     return 0
 
@@ -241,6 +272,14 @@ def main():
         _cabi.check(lib.ngp_render_host(h, _cabi.ptr(o_pin), _cabi.ptr(d_pin), N, 0.0, 1024, 1.0, _cabi.ptr(img_pin), _cabi.ptr(dep_pin),
                                         _cabi.stream()), "ngp_render_host")
 
+    pose_pin = None
+    if n_frames == 1:   # single-camera workloads: the same frame from its 4x4 pose (64 B up instead of 24 B per ray)
+        pose_pin = torch.from_numpy(np.asarray(syn.orbit_pose(37.0 + 45.0 * rank), np.float32)[None].copy()).pin_memory()
+
+    def render_pose_host():
+        model.render_poses_host(pose_pin, (wl["focal"], wl["focal"], wl["W"] / 2, wl["H"] / 2), wl["H"], wl["W"], image=img_pin, depth=dep_pin,
+                                dt_gamma=0, bg_color=1, max_steps=1024)
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -284,10 +323,16 @@ def main():
         launches = _cabi.launch_count() - launches0
         ms_e2e = timed(render_host, args.steps, host_timer=True)
         barrier()
+        ms_pose = None
+        if pose_pin is not None:
+            render_pose_host()
+            ms_pose = timed(render_pose_host, args.steps, host_timer=True)
+            barrier()
     if world > 1:
-        t = torch.tensor([ms_dev, ms_e2e], dtype=torch.float64, device=dev)
+        t = torch.tensor([ms_dev, ms_e2e, ms_pose or 0.0], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e = t.tolist()
+        ms_dev, ms_e2e, ms_pose = t.tolist()
+        ms_pose = ms_pose or None
         cnt = torch.tensor([N, samples], dtype=torch.int64, device=dev)
         dist.all_reduce(cnt)
         rays_all, samples_all = cnt.tolist()
@@ -317,6 +362,10 @@ def main():
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(o_pin.numel() * 4 + d_pin.numel() * 4),
                         "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_e2e / args.steps,
                         "api": "ngp_render_host (C ABI, pinned host buffers)"},
+                "e2e_from_pose": None if not ms_pose else {
+                    "value": rays_all / (ms_pose / args.steps * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 64,
+                    "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_pose / args.steps,
+                    "api": "ngp_render_poses_host (C ABI: host 4x4 pose in, rays generated on the device by ngp_get_rays, host image + depth out)"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                              "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload), "kernel": "k_render", "algorithmic_bytes_per_sample": 512,
@@ -329,10 +378,14 @@ def main():
                 "clocks": clocks.summary()}
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            n = args.cpu_rays or 20000
+            n = args.cpu_rays or 100000
             v, dt, rays, _ = cpu_port_mrays(wl, args.variant, n)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port", "seconds": dt,
                                     "sample": f"{rays} rays (strided sub-sample of the same frame), oracle/ngp_oracle.c, OpenMP"}
+            try:
+                line["cpu_reference_run"] = cpu_run_sampler_mrays()
+            except Exception as e:
+                line["cpu_reference_run"] = {"unavailable": f"{type(e).__name__}: {e}"}
         if world == 1 and not args.no_ref_gpu:
             line["reference_gpu"] = reference_gpu(wl, w, bitfield, o_dev, d_dev, flush, dev)
         print(json.dumps(line))

@@ -46,6 +46,11 @@ uint64_t ngp_launch_count(void);
 /* raymarching/src/raymarching.cu:93-158.  aabb: device float[6]. Misses write FLT_MAX to both. */
 int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, uint32_t N,
                            float min_near, float *nears, float *fars, void *stream);
+/* nerf/utils.py:52-116 (get_rays, N = -1: every pixel, centres at +0.5): poses = device float [F,4,4] row-major cam2world,
+ * rays_o / rays_d = device float [F, H*W, 3].  Replaces the meshgrid + stack + norm + matmul ATen sequence the reference runs
+ * before every render (validate.py:290 -> nav/estimator_helpers.py:236-243). */
+int ngp_get_rays(const float *poses, uint32_t F, uint32_t H, uint32_t W, float fx, float fy, float cx, float cy,
+                 float *rays_o, float *rays_d, void *stream);
 /* raymarching/src/raymarching.cu:216-235 */
 int ngp_morton3D(const int32_t *coords, uint32_t N, int32_t *indices, void *stream);
 /* raymarching/src/raymarching.cu:240-262 */
@@ -136,6 +141,13 @@ int ngp_render(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t 
 int ngp_render_host(ngp_ctx *ctx, const float *rays_o_host, const float *rays_d_host, uint32_t N,
                     float dt_gamma, uint32_t max_steps, float bg_color, float *image_host, float *depth_host,
                     void *stream);
+
+/* Estimator.render_from_pose (nav/estimator_helpers.py:236-243) for a batch of F cameras: HOST poses [F,4,4] in (64 B per
+ * frame instead of 24 B per ray), rays generated on the device (ngp_get_rays), one render over all F*H*W rays (one n_step
+ * schedule, exactly like renderer.py:265-269 flattens a [F,N,3] batch), HOST image [F*H*W,3] / depth [F*H*W] out; synchronous. */
+int ngp_render_poses_host(ngp_ctx *ctx, const float *poses_host, uint32_t F, uint32_t H, uint32_t W, float fx, float fy,
+                          float cx, float cy, float dt_gamma, uint32_t max_steps, float bg_color, float *image_host,
+                          float *depth_host, void *stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -17,6 +17,7 @@ _SIGNATURES = {
     "ngp_last_error": [],
     "ngp_launch_count": [],
     "ngp_near_far_from_aabb": [_p, _p, _p, _u32, _f32, _p, _p, _p],
+    "ngp_get_rays": [_p, _u32, _u32, _u32, _f32, _f32, _f32, _f32, _p, _p, _p],
     "ngp_morton3D": [_p, _u32, _p, _p],
     "ngp_morton3D_invert": [_p, _u32, _p, _p],
     "ngp_packbits": [_p, _u32, _f32, _p, _p],
@@ -38,6 +39,7 @@ _SIGNATURES = {
     "ngp_network_forward_tc": [_p, _p, _p, _u32, _i32, _p, _p, _p],
     "ngp_render": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render_host": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p],
+    "ngp_render_poses_host": [_p, _p, _u32, _u32, _u32, _f32, _f32, _f32, _f32, _f32, _u32, _f32, _p, _p, _p],
 }
 _RESTYPES = {"ngp_last_error": C.c_char_p, "ngp_launch_count": _u64, "ngp_compact_scratch_bytes": _u64}
 

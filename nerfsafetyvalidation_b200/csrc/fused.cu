@@ -884,6 +884,8 @@ struct ngp_ctx {
     // staging for ngp_render_host
     uint32_t capHost = 0;
     float *d_o = nullptr, *d_d = nullptr, *d_img = nullptr, *d_depth = nullptr, *d_ws = nullptr;
+    float *d_poses = nullptr;     // staging for ngp_render_poses_host
+    uint32_t capPoses = 0;
     uint32_t *coarse = nullptr;   // 4x4x4-block occupancy bits, rebuilt from the borrowed bitfield at every ngp_render
     uint32_t coarse_words = 0;
     long long *prof = nullptr;    // device [8], allocated by ngp_ctx_enable_profile
@@ -918,7 +920,7 @@ int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
     cudaFree(c->wpack); cudaFree(c->wtc); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
     cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
-    cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
+    cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws); cudaFree(c->d_poses);
     delete c;
     return 0;
 }
@@ -1133,11 +1135,7 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     return after_launch("render");
 }
 
-int ngp_render_host(ngp_ctx *c, const float *rays_o_host, const float *rays_d_host, uint32_t N, float dt_gamma, uint32_t max_steps,
-                    float bg_color, float *image_host, float *depth_host, void *stream) {
-    NGP_REQUIRE(c != nullptr, "render_host: null ctx");
-    NGP_REQUIRE(rays_o_host && rays_d_host && image_host && depth_host, "render_host: null host pointer");
-    if (N == 0) return 0;
+static int ensure_host_staging(ngp_ctx *c, uint32_t N) {
     if (N > c->capHost) {
         cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
         c->capHost = 0;
@@ -1148,9 +1146,43 @@ int ngp_render_host(ngp_ctx *c, const float *rays_o_host, const float *rays_d_ho
         NGP_CUDA(cudaMalloc(&c->d_ws, sizeof(float) * (size_t)N));
         c->capHost = N;
     }
+    return 0;
+}
+
+int ngp_render_host(ngp_ctx *c, const float *rays_o_host, const float *rays_d_host, uint32_t N, float dt_gamma, uint32_t max_steps,
+                    float bg_color, float *image_host, float *depth_host, void *stream) {
+    NGP_REQUIRE(c != nullptr, "render_host: null ctx");
+    NGP_REQUIRE(rays_o_host && rays_d_host && image_host && depth_host, "render_host: null host pointer");
+    if (N == 0) return 0;
+    if (int rc = ensure_host_staging(c, N)) return rc;
     cudaStream_t st = as_stream(stream);
     NGP_CUDA(cudaMemcpyAsync(c->d_o, rays_o_host, sizeof(float) * 3 * (size_t)N, cudaMemcpyHostToDevice, st));
     NGP_CUDA(cudaMemcpyAsync(c->d_d, rays_d_host, sizeof(float) * 3 * (size_t)N, cudaMemcpyHostToDevice, st));
+    if (int rc = ngp_render(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, c->d_img, c->d_depth, c->d_ws, nullptr, nullptr, stream)) return rc;
+    NGP_CUDA(cudaMemcpyAsync(image_host, c->d_img, sizeof(float) * 3 * (size_t)N, cudaMemcpyDeviceToHost, st));
+    NGP_CUDA(cudaMemcpyAsync(depth_host, c->d_depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st));
+    NGP_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int ngp_render_poses_host(ngp_ctx *c, const float *poses_host, uint32_t F, uint32_t H, uint32_t W, float fx, float fy, float cx, float cy,
+                          float dt_gamma, uint32_t max_steps, float bg_color, float *image_host, float *depth_host, void *stream) {
+    NGP_REQUIRE(c != nullptr, "render_poses_host: null ctx");
+    NGP_REQUIRE(poses_host && image_host && depth_host, "render_poses_host: null host pointer");
+    const unsigned long long n = (unsigned long long)F * H * W;
+    if (n == 0) return 0;
+    NGP_REQUIRE(n <= 0xffffffffull, "render_poses_host: %llu rays exceed the 32-bit ray index of the renderer", n);
+    const uint32_t N = (uint32_t)n;
+    if (int rc = ensure_host_staging(c, N)) return rc;
+    if (F > c->capPoses) {
+        cudaFree(c->d_poses);
+        c->capPoses = 0;
+        NGP_CUDA(cudaMalloc(&c->d_poses, sizeof(float) * 16 * (size_t)F));
+        c->capPoses = F;
+    }
+    cudaStream_t st = as_stream(stream);
+    NGP_CUDA(cudaMemcpyAsync(c->d_poses, poses_host, sizeof(float) * 16 * (size_t)F, cudaMemcpyHostToDevice, st));   // 64 B per frame
+    if (int rc = ngp_get_rays(c->d_poses, F, H, W, fx, fy, cx, cy, c->d_o, c->d_d, stream)) return rc;
     if (int rc = ngp_render(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, c->d_img, c->d_depth, c->d_ws, nullptr, nullptr, stream)) return rc;
     NGP_CUDA(cudaMemcpyAsync(image_host, c->d_img, sizeof(float) * 3 * (size_t)N, cudaMemcpyDeviceToHost, st));
     NGP_CUDA(cudaMemcpyAsync(depth_host, c->d_depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st));

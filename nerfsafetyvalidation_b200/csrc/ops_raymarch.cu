@@ -24,6 +24,29 @@ __global__ void __launch_bounds__(kThreads) k_near_far(const float *__restrict__
     fars[n] = far;
 }
 
+// nerf/utils.py:52-116 (N = -1: every pixel): pixel centre (+0.5) -> camera direction ((i - cx) / fx, (j - cy) / fy, 1), normalised,
+// rotated by the cam2world pose; origin = pose translation.  One thread per ray; poses [F,4,4] row-major.  Operation order is fixed
+// (IEEE mul / add / div / sqrt, no contraction) so the oracle reproduces it bit for bit; torch's norm + cuBLAS matmul agree to 1 ulp.
+__global__ void __launch_bounds__(kThreads) k_get_rays(const float *__restrict__ poses, uint32_t F, uint32_t H, uint32_t W, float fx, float fy,
+                                                       float cx, float cy, float *__restrict__ rays_o, float *__restrict__ rays_d) {
+    const size_t n = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t HW = H * W;
+    if (n >= (size_t)F * HW) return;
+    const uint32_t f = (uint32_t)(n / HW), p = (uint32_t)(n % HW);
+    const float *P = poses + (size_t)f * 16;
+    const float i = __fadd_rn((float)(p % W), 0.5f), j = __fadd_rn((float)(p / W), 0.5f);
+    const float x = __fdiv_rn(__fsub_rn(i, cx), fx), y = __fdiv_rn(__fsub_rn(j, cy), fy);
+    const float nrm = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), 1.0f));
+    const float d0 = __fdiv_rn(x, nrm), d1 = __fdiv_rn(y, nrm), d2 = __fdiv_rn(1.0f, nrm);
+    float *o = rays_o + n * 3, *d = rays_d + n * 3;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float r0 = __ldg(P + 4 * k), r1 = __ldg(P + 4 * k + 1), r2 = __ldg(P + 4 * k + 2);
+        d[k] = __fadd_rn(__fadd_rn(__fmul_rn(d0, r0), __fmul_rn(d1, r1)), __fmul_rn(d2, r2));
+        o[k] = __ldg(P + 4 * k + 3);
+    }
+}
+
 // raymarching/src/raymarching.cu:216-262
 __global__ void __launch_bounds__(kThreads) k_morton3d(const int *__restrict__ coords, uint32_t N, int *__restrict__ indices) {
     const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -160,6 +183,17 @@ int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float
     NGP_DEVPTR(rays_o); NGP_DEVPTR(rays_d); NGP_DEVPTR(aabb); NGP_DEVPTR(nears); NGP_DEVPTR(fars);
     k_near_far<<<div_up(N, kThreads), kThreads, 0, as_stream(stream)>>>(rays_o, rays_d, aabb, N, min_near, nears, fars);
     return after_launch("near_far_from_aabb");
+}
+
+int ngp_get_rays(const float *poses, uint32_t F, uint32_t H, uint32_t W, float fx, float fy, float cx, float cy, float *rays_o,
+                 float *rays_d, void *stream) {
+    const unsigned long long n = (unsigned long long)F * H * W;
+    if (n == 0) return 0;
+    NGP_REQUIRE(n <= 0xffffffffull, "get_rays: %llu rays exceed the 32-bit ray index of the renderer", n);
+    NGP_REQUIRE(fx != 0.f && fy != 0.f, "get_rays: zero focal length");
+    NGP_DEVPTR(poses); NGP_DEVPTR(rays_o); NGP_DEVPTR(rays_d);
+    k_get_rays<<<div_up((uint32_t)n, kThreads), kThreads, 0, as_stream(stream)>>>(poses, F, H, W, fx, fy, cx, cy, rays_o, rays_d);
+    return after_launch("get_rays");
 }
 
 int ngp_morton3D(const int32_t *coords, uint32_t N, int32_t *indices, void *stream) {

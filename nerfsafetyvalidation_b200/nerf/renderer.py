@@ -203,6 +203,42 @@ class NeRFRenderer(nn.Module):
         return self.run_cuda(rays_o, rays_d, **kwargs)
 
     @torch.no_grad()
+    def render_poses(self, poses, intrinsics, H, W, **kwargs):
+        """Estimator.render_from_pose (nav/estimator_helpers.py:236-243) for a batch: poses [F,4,4] cam2world (CUDA, NGP frame),
+        intrinsics (fx, fy, cx, cy) -> render() result with image [F, H*W, 3], depth [F, H*W].  Rays are generated on the device
+        by ngp_get_rays (nerf/utils.py:52-116)."""
+        from .utils import get_rays
+        r = get_rays(poses, intrinsics, H, W)
+        return self.render(r["rays_o"], r["rays_d"], **kwargs)
+
+    @torch.no_grad()
+    def render_poses_host(self, poses, intrinsics, H, W, image=None, depth=None, dt_gamma=0, bg_color=1, max_steps=1024):
+        """The same through ONE C-ABI call with HOST buffers (ngp_render_poses_host): poses = CPU float32 tensor [F,4,4] (64 B per
+        frame go up instead of 24 B per ray), image [F*H*W,3] / depth [F*H*W] = CPU float32 tensors (pinned for full PCIe speed;
+        allocated if None).  Synchronous.  Returns (image, depth)."""
+        if self.training or self.bg_radius > 0 or not self.cuda_ray:
+            raise NotImplementedError("render_poses_host serves the cuda_ray inference path (model.eval(), bg_radius <= 0)")
+        if not self._configure_native(self._native):
+            raise RuntimeError("render_poses_host: this model cannot be served by the fused renderer")
+        poses = poses.detach().to(torch.float32).contiguous()
+        if poses.is_cuda or tuple(poses.shape[1:]) != (4, 4):
+            raise RuntimeError("render_poses_host: poses must be a CPU tensor [F,4,4] (use render_poses for device poses)")
+        F = poses.shape[0]
+        n = F * H * W
+        image = torch.empty(n, 3, dtype=torch.float32).pin_memory() if image is None else image
+        depth = torch.empty(n, dtype=torch.float32).pin_memory() if depth is None else depth
+        for t, shape in ((image, (n, 3)), (depth, (n,))):
+            if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous() or tuple(t.shape) != shape:
+                raise RuntimeError(f"render_poses_host: output buffers must be contiguous CPU float32 {shape}")
+        lib = _cabi.load()
+        handle = self._native.get()
+        self._set_scene(self._native, handle)
+        fx, fy, cx, cy = (float(v) for v in intrinsics)
+        _cabi.check(lib.ngp_render_poses_host(handle, _cabi.ptr(poses), F, H, W, fx, fy, cx, cy, float(dt_gamma), int(max_steps),
+                                              float(bg_color), _cabi.ptr(image), _cabi.ptr(depth), _cabi.stream()), "ngp_render_poses_host")
+        return image, depth
+
+    @torch.no_grad()
     def mark_untrained_grid(self, poses, intrinsic, S=64):
         raise NotImplementedError("mark_untrained_grid belongs to training-time occupancy maintenance (SURVEY.md section 8f row 4)")
 

@@ -1,6 +1,8 @@
 """The two helpers of the reference's nerf/utils.py that sit on the render path: `custom_meshgrid`, `get_rays`."""
 import torch
 
+from .. import _cabi
+
 
 def custom_meshgrid(*args):
     """nerf/utils.py:33-38"""
@@ -10,21 +12,19 @@ def custom_meshgrid(*args):
 @torch.no_grad()
 def get_rays(poses, intrinsics, H, W, N=-1, error_map=None):
     """nerf/utils.py:52-116 for the inference case (N <= 0: every pixel, pixel centres at +0.5).
-    poses [B,4,4] cam2world, intrinsics (fx, fy, cx, cy) -> dict(rays_o [B,H*W,3], rays_d [B,H*W,3])."""
+    poses [B,4,4] cam2world (CUDA), intrinsics (fx, fy, cx, cy) -> dict(rays_o [B,H*W,3], rays_d [B,H*W,3]).
+    One kernel (ngp_get_rays) instead of the reference's meshgrid / stack / norm / matmul sequence; no CPU fallback."""
     if N > 0:
         raise NotImplementedError("get_rays: random pixel sub-sampling (N > 0) is the training path")
-    device = poses.device
+    _cabi.require_cuda(poses)
+    fx, fy, cx, cy = (float(v) for v in intrinsics)
+    poses = poses.detach().to(torch.float32).contiguous()
     B = poses.shape[0]
-    fx, fy, cx, cy = intrinsics
-    i, j = custom_meshgrid(torch.linspace(0, W - 1, W, device=device), torch.linspace(0, H - 1, H, device=device))
-    i = i.t().reshape([1, H * W]).expand([B, H * W]) + 0.5
-    j = j.t().reshape([1, H * W]).expand([B, H * W]) + 0.5
-    zs = torch.ones_like(i)
-    xs = (i - cx) / fx * zs
-    ys = (j - cy) / fy * zs
-    directions = torch.stack((xs, ys, zs), dim=-1)
-    directions = directions / torch.norm(directions, dim=-1, keepdim=True)
-    rays_d = directions @ poses[:, :3, :3].transpose(-1, -2)
-    rays_o = poses[..., :3, 3]
-    rays_o = rays_o[..., None, :].expand_as(rays_d)
+    if tuple(poses.shape[1:]) != (4, 4):
+        raise RuntimeError(f"get_rays: poses must be [B,4,4], got {tuple(poses.shape)}")
+    rays_o = torch.empty(B, H * W, 3, dtype=torch.float32, device=poses.device)
+    rays_d = torch.empty(B, H * W, 3, dtype=torch.float32, device=poses.device)
+    with torch.cuda.device(poses.device):
+        _cabi.check(_cabi.load().ngp_get_rays(_cabi.ptr(poses), B, H, W, fx, fy, cx, cy, _cabi.ptr(rays_o), _cabi.ptr(rays_d), _cabi.stream()),
+                    "ngp_get_rays")
     return {"rays_o": rays_o, "rays_d": rays_d}

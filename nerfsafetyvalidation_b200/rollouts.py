@@ -216,16 +216,10 @@ def cem_update(risks_local, noise_local, ids_local, n_rollouts, m_elite, p_mean,
 
 # ------------------------------------------------------------------ GPU drivers (one process per GPU; weights replicated)
 def get_rays_device(poses, fx, fy, cx, cy, H, W):
-    """get_rays (nerf/utils.py:52-116) with torch ops on poses' device: [B,4,4] -> rays_o, rays_d [B, H*W, 3] fp32."""
-    import torch
-    dev = poses.device
-    j, i = torch.meshgrid(torch.arange(H, dtype=torch.float32, device=dev) + 0.5, torch.arange(W, dtype=torch.float32, device=dev) + 0.5,
-                          indexing="ij")
-    d = torch.stack(((i.reshape(-1) - cx) / fx, (j.reshape(-1) - cy) / fy, torch.ones(H * W, device=dev)), -1)
-    d = d / torch.norm(d, dim=-1, keepdim=True)
-    rays_d = d @ poses[:, :3, :3].transpose(-1, -2)
-    rays_o = poses[:, None, :3, 3].expand_as(rays_d)
-    return rays_o.contiguous(), rays_d.contiguous()
+    """get_rays (nerf/utils.py:52-116) on poses' device with the ngp_get_rays kernel: [B,4,4] -> rays_o, rays_d [B, H*W, 3] fp32."""
+    from .nerf.utils import get_rays as get_rays_cuda
+    r = get_rays_cuda(poses, (fx, fy, cx, cy), H, W)
+    return r["rays_o"], r["rays_d"]
 
 
 def render_rollouts(model, ids, steps, H, W, focal, frames_per_call=64, mean=None, std=None, **render_kw):

@@ -129,6 +129,11 @@ int ngp_network_forward(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint
 /* Same contract as ngp_network_forward, both MLPs on tcgen05 (128-row tiles, accumulators in tensor memory). */
 int ngp_network_forward_tc(ngp_ctx *ctx, const float *xyzs, const float *dirs, uint32_t M, int apply_density_scale,
                            float *sigmas, float *rgbs, void *stream);
+/* NeRFNetwork.density (nerf/network_ff.py:76-89; `density_fn` of validate.py:288, the planner's and update_extra_state's query) in
+ * one kernel: xyzs [M,3] fp32 -> sigmas [M] fp32 = exp(h0) (x density_scale if apply_density_scale != 0) and, if geo_feat_f16
+ * is not NULL, geo_feat [M,15] half = h[1:16].  Hash-grid gather + sigma net on tcgen05; nothing else touches HBM. */
+int ngp_density_forward(ngp_ctx *ctx, const float *xyzs, uint32_t M, int apply_density_scale, float *sigmas,
+                        void *geo_feat_f16, void *stream);
 /* NeRFRenderer.run_cuda, inference branch (nerf/renderer.py:261-284,329-386) as ONE persistent launch:
  * near/far -> loop{march -> encode -> MLPs -> composite -> stable compaction, global n_step schedule} ->
  * background mix + depth normalisation.  image [N,3], depth [N], weights_sum [N] fp32 (any may not be NULL).

@@ -37,6 +37,7 @@ _SIGNATURES = {
     "ngp_ctx_phase_cycles": [_p, _p, _i32],
     "ngp_network_forward": [_p, _p, _p, _u32, _i32, _p, _p, _p],
     "ngp_network_forward_tc": [_p, _p, _p, _u32, _i32, _p, _p, _p],
+    "ngp_density_forward": [_p, _p, _u32, _i32, _p, _p, _p],
     "ngp_render": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render_host": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p],
     "ngp_render_poses_host": [_p, _p, _u32, _u32, _u32, _f32, _f32, _f32, _f32, _f32, _u32, _f32, _p, _p, _p],

@@ -104,7 +104,11 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
     }
     // the trip loop is deliberately NOT unrolled: a 4x smaller gather body keeps the renderer's warps, which sit in different
     // phases, inside the instruction cache
-#pragma unroll 1
+#ifndef NGP_TRIP_UNROLL
+#define NGP_TRIP_UNROLL 1
+#endif
+    constexpr int kTripUnroll = NGP_TRIP_UNROLL;
+#pragma unroll kTripUnroll
     for (int grp = 0; grp < 4; grp++) dst[grp * stride] = encode_trip(nc, u0, u1, u2, grp);
 }
 
@@ -272,8 +276,10 @@ __global__ void k_pack_network_tc(const __half *__restrict__ w_sigma, uint32_t n
 }
 
 // network_ff.py:51-74 with both MLPs on tcgen05: one warpgroup per CTA, thread = row of a 128-row tile.
+//   kDensityOnly: NeRFNetwork.density (network_ff.py:76-89) -- encoder + sigma net; `rgbs` is then a half [M,15] geo_feat buffer or NULL.
+template <bool kDensityOnly>
 __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const float *__restrict__ xyzs, const float *__restrict__ dirs, uint32_t M,
-                                                            float *__restrict__ sigmas, float *__restrict__ rgbs, uint32_t n_tiles) {
+                                                            float *__restrict__ sigmas, void *__restrict__ rgbs_or_geo, uint32_t n_tiles) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
     uint4 *s_a = s_w + nc.wtc_bytes / 16;
@@ -300,16 +306,30 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
         uint4 sh_lo = make_uint4(0, 0, 0, 0), sh_hi = sh_lo;
         if (row < M) {
             encode_point(nc, __ldg(xyzs + (size_t)row * 3), __ldg(xyzs + (size_t)row * 3 + 1), __ldg(xyzs + (size_t)row * 3 + 2), s_a + tid, tc::kRows);
-            sh_to_half(__ldg(dirs + (size_t)row * 3), __ldg(dirs + (size_t)row * 3 + 1), __ldg(dirs + (size_t)row * 3 + 2), sh_lo, sh_hi);
+            if (!kDensityOnly)
+                sh_to_half(__ldg(dirs + (size_t)row * 3), __ldg(dirs + (size_t)row * 3 + 1), __ldg(dirs + (size_t)row * 3 + 2), sh_lo, sh_hi);
         } else {
             s_a[tid] = s_a[tc::kRows + tid] = s_a[2 * tc::kRows + tid] = s_a[3 * tc::kRows + tid] = make_uint4(0, 0, 0, 0);
         }
-        float sg, r, g, b;
-        tc::mlp_tile128(t, tid, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, r, g, b);
-        if (row < M) {
-            sigmas[row] = sg;
-            float *o = rgbs + (size_t)row * 3;
-            o[0] = r; o[1] = g; o[2] = b;
+        if (kDensityOnly) {
+            float h[16];
+            tc::sigma_tile128(t, tid, nc.nh_sigma, h);
+            if (row < M) {
+                sigmas[row] = expf(h[0]) * nc.density_scale;   // trunc_exp of the half output, in fp32 (activation.py:5-18)
+                if (rgbs_or_geo) {
+                    __half *o = reinterpret_cast<__half *>(rgbs_or_geo) + (size_t)row * 15;
+#pragma unroll
+                    for (int i = 0; i < 15; i++) o[i] = __float2half_rn(h[i + 1]);
+                }
+            }
+        } else {
+            float sg, r, g, b;
+            tc::mlp_tile128(t, tid, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, r, g, b);
+            if (row < M) {
+                sigmas[row] = sg;
+                float *o = reinterpret_cast<float *>(rgbs_or_geo) + (size_t)row * 3;
+                o[0] = r; o[1] = g; o[2] = b;
+            }
         }
     }
     tc::fence_before_sync();
@@ -979,7 +999,8 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
         nc.wtc = c->wtc;
         nc.wtc_bytes = wm.total;
         c->fwd_tc_smem = wm.total + 8 * tc::kRows * 16 + 16;
-        NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
+        NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
+        NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
     }
     c->fwd_smem = fwd_smem_bytes(nc);
     c->render_smem = render_smem_bytes(nc);
@@ -1066,8 +1087,22 @@ int ngp_network_forward_tc(ngp_ctx *c, const float *xyzs, const float *dirs, uin
     const uint32_t grid = n_tiles < cap ? n_tiles : cap;
     NetConst nc = c->nc;
     if (!apply_density_scale) nc.density_scale = 1.0f;
-    k_network_forward_tc<<<grid, tc::kRows, c->fwd_tc_smem, as_stream(stream)>>>(nc, xyzs, dirs, M, sigmas, rgbs, n_tiles);
+    k_network_forward_tc<false><<<grid, tc::kRows, c->fwd_tc_smem, as_stream(stream)>>>(nc, xyzs, dirs, M, sigmas, rgbs, n_tiles);
     return after_launch("network_forward_tc");
+}
+
+int ngp_density_forward(ngp_ctx *c, const float *xyzs, uint32_t M, int apply_density_scale, float *sigmas, void *geo_feat_f16, void *stream) {
+    NGP_REQUIRE(c != nullptr && c->has_net, "density_forward: ngp_ctx_set_network has not been called");
+    if (M == 0) return 0;
+    NGP_DEVPTR(xyzs); NGP_DEVPTR(sigmas);
+    if (geo_feat_f16) NGP_DEVPTR(geo_feat_f16);
+    const uint32_t n_tiles = div_up(M, (uint32_t)tc::kRows);
+    const uint32_t cap = (uint32_t)c->sm_count * 4;
+    const uint32_t grid = n_tiles < cap ? n_tiles : cap;
+    NetConst nc = c->nc;
+    if (!apply_density_scale) nc.density_scale = 1.0f;
+    k_network_forward_tc<true><<<grid, tc::kRows, c->fwd_tc_smem, as_stream(stream)>>>(nc, xyzs, nullptr, M, sigmas, geo_feat_f16, n_tiles);
+    return after_launch("density_forward");
 }
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {

@@ -240,6 +240,23 @@ __device__ __forceinline__ void mlp_tile128(Tile &t, int row, uint32_t nh_sigma,
     }
 }
 
+// The density net alone for the 128 rows of one warpgroup (NeRFNetwork.density, network_ff.py:76-89).  Same precondition as
+// mlp_tile128.  h[16]: the row's sigma-net outputs rounded to half as the reference's FFMLP stores them (h[0] = log-density,
+// h[1..15] = geo_feat).
+__device__ __forceinline__ void sigma_tile128(Tile &t, int row, uint32_t nh_sigma, float (&h)[16]) {
+    const WeightMap wm = weight_map(nh_sigma, 0);
+    layer_mma(t, row, wm.s0, 64, 32);
+    relu_row_to_a(t, row);
+    for (uint32_t k = 0; k < nh_sigma; k++) {
+        layer_mma(t, row, wm.sh + k * 8 * 64 * 16, 64, 64);
+        relu_row_to_a(t, row);
+    }
+    layer_mma(t, row, wm.sl, 16, 64);
+    tmem_ld16(t.tmem, h);
+#pragma unroll
+    for (int i = 0; i < 16; i++) h[i] = __half2float(__float2half_rn(h[i]));
+}
+
 // ---- pipelined variant: issue and completion of a layer are split, so that the caller can do independent work (the next pass's
 //      gather) while the tensor core runs and while the other warps of the group catch up.  No thread waits at a barrier:
 //        every warp     : stores its rows, fence.proxy.async, then ONE arrive on `aready` (count 4)

@@ -100,7 +100,18 @@ class NeRFNetwork(NeRFRenderer):
         return sigma, rgb
 
     def density(self, x):
-        """network_ff.py:76-89"""
+        """network_ff.py:76-89: x [N,3] -> {'sigma' [N] fp32, 'geo_feat' [N,15] half}.  One kernel (ngp_density_forward: hash-grid
+        gather + sigma net on tcgen05) when the model is the fusable NGP configuration; the stand-alone ops otherwise."""
+        if getattr(self, "fused_density", True) and self._configure_native(self._native):
+            _cabi.require_cuda(x)
+            prefix = x.shape[:-1]
+            x = x.float().contiguous().view(-1, 3)
+            M = x.shape[0]
+            sigma = torch.empty(M, dtype=torch.float32, device=x.device)
+            geo = torch.empty(M, self.geo_feat_dim, dtype=torch.float16, device=x.device)
+            _cabi.check(_cabi.load().ngp_density_forward(self._native.get(), _cabi.ptr(x), M, 0, _cabi.ptr(sigma), _cabi.ptr(geo),
+                                                         _cabi.stream()), "ngp_density_forward")
+            return {"sigma": sigma.view(*prefix), "geo_feat": geo.view(*prefix, self.geo_feat_dim)}
         x = self.encoder(x, bound=self.bound)
         h = self.sigma_net(x)
         sigma = trunc_exp(h[..., 0])

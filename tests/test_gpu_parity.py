@@ -341,6 +341,45 @@ def test_network_forward(frame, cuda, variant):
         assert (rgb - rr.float()).abs().max().item() <= 4e-3, "rgb vs reference ext"
 
 
+@pytest.mark.parametrize("variant", ["A", "B"])
+def test_density_query(frame, cuda, variant):
+    """NeRFNetwork.density (network_ff.py:76-89): the fused kernel against forward()'s sigma (identical
+    arithmetic: bit-exact), against the composition of the stand-alone ops, and against the reference extensions."""
+    ours = frame["ours" + variant]
+    g = torch.Generator().manual_seed(5)
+    x = (torch.rand(30001, 3, generator=g) * 2 - 1).to(cuda)
+    x[:8] = 0.0
+    x[8:16] = 1.5         # outside the box: the encoding is all zeros (gridencoder.cu:99-123)
+    d = torch.zeros_like(x)
+    d[:, 2] = 1.0
+    before = _cabi.launch_count()
+    with torch.no_grad():
+        out = ours.density(x)
+        sig_f, _ = ours(x, d)
+    assert _cabi.launch_count() - before == 2                      # one kernel per call
+    assert out["sigma"].shape == (30001,) and out["geo_feat"].shape == (30001, 15) and out["geo_feat"].dtype == torch.float16
+    assert torch.equal(out["sigma"], sig_f)
+    ours.fused_density = False
+    try:
+        with torch.no_grad():
+            u = ours.density(x)
+    finally:
+        ours.fused_density = True
+    assert ((out["sigma"] - u["sigma"].float()).abs() / u["sigma"].float().abs().clamp_min(1e-6)).max().item() <= 2e-2
+    gmax = max(1.0, u["geo_feat"].float().abs().max().item())
+    assert (out["geo_feat"].float() - u["geo_feat"].float()).abs().max().item() <= 4e-3 * gmax
+    for M in (0, 1, 127, 129):
+        with torch.no_grad():
+            o = ours.density(x[:M])
+        assert torch.equal(o["sigma"], out["sigma"][:M]) and torch.equal(o["geo_feat"], out["geo_feat"][:M])
+    with torch.no_grad():
+        o3 = ours.density(x[:600].view(20, 30, 3))                # leading dimensions are kept, like the reference's
+    assert o3["sigma"].shape == (20, 30) and o3["geo_feat"].shape == (20, 30, 15)
+    if refext.available():
+        rs, _ = frame["ref" + variant].forward(x, d)
+        assert ((out["sigma"] - rs).abs() / rs.abs().clamp_min(1e-6)).max().item() <= 2e-2, "sigma vs reference ext"
+
+
 # ---------------------------------------------------------------------------------------------- end to end
 def render_ours(model, o, d, **kw):
     with torch.no_grad():

@@ -226,6 +226,12 @@ def main():
     if args.impl == "reference":
         return run_reference_arm(args, wl)
 
+    # stdout carries exactly ONE line (the JSON): anything libraries print there (NCCL's version banner under NCCL_DEBUG, ...)
+    # goes to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
 
@@ -388,7 +394,8 @@ def main():
                 line["cpu_reference_run"] = {"unavailable": f"{type(e).__name__}: {e}"}
         if world == 1 and not args.no_ref_gpu:
             line["reference_gpu"] = reference_gpu(wl, w, bitfield, o_dev, d_dev, flush, dev)
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -594,9 +594,15 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
             const float4 ca = sa;
             const float cb = sb;
             if (!dead && i + K < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i0 + K) * R); sb = __ldcs(ra.smp_b + tbase + (size_t)(i0 + K) * R); }
+#ifndef NGP_ABLATE_GATHER   // ablation builds (tools/ab_build.sh): what does the frame cost without one of the two big phases?
             if (active) encode_point(nc, ca.x, ca.y, ca.z, erow, tc::kRows);
+#endif
             NGP_PROF(3)
+#ifndef NGP_ABLATE_MLP
             tc::mlp_tile128_pipelined(tt, wg_tid, lane, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, cr, cg, cbl, [](int) {});
+#else
+            sg = 1.0f + __uint_as_float(sh_lo.x & 1u); cr = cg = cbl = 0.5f;
+#endif
             if (K == 1) {
                 if (active && composite_sample(a, sg, cr, cg, cbl, ca.w, cb)) {   // raymarching.cu:866-894
                     dead = true;
@@ -686,7 +692,11 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     if (tid == 0) {
         for (int g = 0; g < kRenderGroups; g++) {
             tc::mbar_init(tc::smem_u32(&s_mbar[g]), 1);
+#ifdef NGP_LAST_ARRIVER
+            s_aready[g] = 0;                                  // arrival counter (tc_mlp.cuh: layer_issue)
+#else
             tc::mbar_init(tc::smem_u32(&s_aready[g]), 4);   // one arrival per warp of the group
+#endif
         }
         tc::mbar_init_fence();
     }

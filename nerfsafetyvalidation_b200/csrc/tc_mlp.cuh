@@ -266,6 +266,27 @@ __device__ __forceinline__ void layer_issue(Tile &t, int row, int lane, uint32_t
     fence_async_smem();      // this thread's A-row stores -> visible to the tensor core's (async proxy) reads
     fence_before_sync();     // this thread's tcgen05.ld of the previous accumulators are ordered before the arrive
     __syncwarp();
+#ifdef NGP_LAST_ARRIVER
+    // the LAST of the four warps to arrive issues the layer: nobody waits for the operand, and the issue happens the moment the
+    // operand is complete.  `aready` is a plain 32-bit arrival counter here (acq_rel at CTA scope: the other warps' stores and
+    // proxy fences happen-before the issuer's MMAs).
+    (void)row;
+    if (lane == 0) {
+        uint32_t old;
+        asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(t.aready_saddr) : "memory");
+        if ((old & 3u) == 3u) {
+            fence_after_sync();
+            const uint32_t idesc = instr_desc(N);
+            const uint32_t tmem_d = t.tmem & 0x0000FFFFu;
+            for (uint32_t k = 0; k < K / 16; k++) {
+                const uint64_t ad = smem_desc(a_saddr + k * 2 * (kRows * 16), kRows * 16, 128);
+                const uint64_t bd = smem_desc(t.w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
+                mma_f16_ss(tmem_d, ad, bd, idesc, k > 0 ? 1u : 0u);
+            }
+            mma_commit(t.mbar_saddr);
+        }
+    }
+#else
     if (lane == 0) mbar_arrive(t.aready_saddr);
     if (row == 0) {
         mbar_wait(t.aready_saddr, t.parity_a);
@@ -280,6 +301,7 @@ __device__ __forceinline__ void layer_issue(Tile &t, int row, int lane, uint32_t
         mma_commit(t.mbar_saddr);
     }
     t.parity_a ^= 1u;
+#endif
     __syncwarp();
 }
 __device__ __forceinline__ void layer_wait(Tile &t) {

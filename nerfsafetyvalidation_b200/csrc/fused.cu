@@ -56,26 +56,33 @@ __device__ __forceinline__ bool encode_unit(const NetConst &nc, float x, float y
     return !((u0 < 0 || u0 > 1) || (u1 < 0 || u1 > 1) || (u2 < 0 || u2 > 1));
 }
 
-// One trip of the gather: levels 4 grp .. 4 grp + 3 of the point (u0, u1, u2) -> 8 halves.  32 independent 4-byte loads in flight.
-__device__ __forceinline__ uint4 encode_trip(const NetConst &nc, float u0, float u1, float u2, int grp) {
-    float f[4][3];
-    __half2 v[4][8];
+// One trip of the gather: levels LPT trip .. LPT trip + LPT - 1 of the point (u0, u1, u2) -> LPT half2 (8 LPT independent 4-byte
+// loads in flight).  LPT = 4 fills one 16-byte operand chunk per trip; LPT = 2 halves the registers a trip holds (builds with
+// more than 16 warps per SM).
+#ifndef NGP_LEVELS_PER_TRIP
+#define NGP_LEVELS_PER_TRIP 2
+#endif
+constexpr int kRenderLevelsPerTrip = NGP_LEVELS_PER_TRIP;   // the renderer: 20 warps per SM at 96 registers (A/B in DESIGN.md section 8)
+
+template <int LPT>
+__device__ __forceinline__ void encode_trip(const NetConst &nc, float u0, float u1, float u2, int trip, uint32_t (&packed)[LPT]) {
+    float f[LPT][3];
+    __half2 v[LPT][8];
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-        const LevelConst &lc = nc.lv[grp * 4 + j];
+    for (int j = 0; j < LPT; j++) {
+        const LevelConst &lc = nc.lv[trip * LPT + j];
         const float scale = lc.scale;
         float p0 = __fmaf_rn(u0, scale, 0.5f), p1 = __fmaf_rn(u1, scale, 0.5f), p2 = __fmaf_rn(u2, scale, 0.5f);
         const uint32_t g0 = (uint32_t)floorf(p0), g1 = (uint32_t)floorf(p1), g2 = (uint32_t)floorf(p2);
         f[j][0] = __fsub_rn(p0, (float)g0); f[j][1] = __fsub_rn(p1, (float)g1); f[j][2] = __fsub_rn(p2, (float)g2);
-        const __half2 *tl = nc.lvbase[grp * 4 + j];
+        const __half2 *tl = nc.lvbase[trip * LPT + j];
         uint32_t row[8];
         cell_rows(lc, g0, g1, g2, row);
 #pragma unroll
         for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
     }
-    uint32_t packed[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
+    for (int j = 0; j < LPT; j++) {
         const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
         const float q0 = 1.0f - p0, q1 = 1.0f - p1, q2 = 1.0f - p2;
         // (w_x * w_y) * w_z, gridencoder.cu:148-160, as packed pairs: (corner 2m, corner 2m + 1) differ in x only
@@ -89,27 +96,29 @@ __device__ __forceinline__ uint4 encode_trip(const NetConst &nc, float u0, float
             const float wk = (k & 1) ? w[k >> 1].y : w[k >> 1].x;
             acc = ffma2(make_float2(wk, wk), __half22float2(v[j][k]), acc);
         }
-        const float a0 = acc.x, a1 = acc.y;
-        packed[j] = pack_half2(a0, a1);
+        packed[j] = pack_half2(acc.x, acc.y);
     }
-    return make_uint4(packed[0], packed[1], packed[2], packed[3]);
 }
 
 // 16-level hash-grid encoding of one point into 16 half2: dst[g * stride], g = 0..3, receives levels 4g .. 4g+3 (8 halves).
+template <int kLevelsPerTrip = 4>
 __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float y, float z, uint4 *dst, int stride = 1) {
+    static_assert(kLevelsPerTrip == 4 || kLevelsPerTrip == 2 || kLevelsPerTrip == 1, "a trip covers a whole, a half or a quarter of a 16-byte operand chunk");
     float u0, u1, u2;
     if (!encode_unit(nc, x, y, z, u0, u1, u2)) {
         dst[0] = dst[stride] = dst[2 * stride] = dst[3 * stride] = make_uint4(0, 0, 0, 0);
         return;
     }
-    // the trip loop is deliberately NOT unrolled: a 4x smaller gather body keeps the renderer's warps, which sit in different
+    // the trip loop is deliberately NOT unrolled: a small gather body keeps the renderer's warps, which sit in different
     // phases, inside the instruction cache
-#ifndef NGP_TRIP_UNROLL
-#define NGP_TRIP_UNROLL 1
-#endif
-    constexpr int kTripUnroll = NGP_TRIP_UNROLL;
-#pragma unroll kTripUnroll
-    for (int grp = 0; grp < 4; grp++) dst[grp * stride] = encode_trip(nc, u0, u1, u2, grp);
+#pragma unroll 1
+    for (int trip = 0; trip < 16 / kLevelsPerTrip; trip++) {
+        uint32_t packed[kLevelsPerTrip];
+        encode_trip<kLevelsPerTrip>(nc, u0, u1, u2, trip, packed);
+        if (kLevelsPerTrip == 4) dst[trip * stride] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        else if (kLevelsPerTrip == 2) reinterpret_cast<uint2 *>(dst + (trip >> 1) * stride)[trip & 1] = make_uint2(packed[0], packed[kLevelsPerTrip - 1]);
+        else reinterpret_cast<uint32_t *>(dst + (trip >> 2) * stride)[trip & 3] = packed[0];
+    }
 }
 
 // degree-4 SH of a direction -> 16 halves (2 x uint4)
@@ -366,7 +375,7 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
 //             accumulators it holds in registers for the whole epoch (raymarching.cu:828-913), early termination included.
 //             Ray state makes one 32-byte round trip per EPOCH; dirs / sigmas / rgbs never exist in memory.
 #ifndef NGP_RENDER_THREADS
-#define NGP_RENDER_THREADS 512
+#define NGP_RENDER_THREADS 640
 #endif
 constexpr int kRenderThreads = NGP_RENDER_THREADS;   // whole warpgroups
 constexpr int kRenderWarps = kRenderThreads / 32;
@@ -595,7 +604,7 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
             const float cb = sb;
             if (!dead && i + K < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i0 + K) * R); sb = __ldcs(ra.smp_b + tbase + (size_t)(i0 + K) * R); }
 #ifndef NGP_ABLATE_GATHER   // ablation builds (tools/ab_build.sh): what does the frame cost without one of the two big phases?
-            if (active) encode_point(nc, ca.x, ca.y, ca.z, erow, tc::kRows);
+            if (active) encode_point<kRenderLevelsPerTrip>(nc, ca.x, ca.y, ca.z, erow, tc::kRows);
 #endif
             NGP_PROF(3)
 #ifndef NGP_ABLATE_MLP

@@ -10,7 +10,8 @@ signatures and result dict (nerf/renderer.py:261-386, 549-588).  Two execution m
   stepwise          the reference's Python loop verbatim, on our stand-alone ops (one launch per op per
                     iteration); kept for kernel-boundary parity tests (`fused=False`).
 
-Only the `cuda_ray=True` eval path is built; training and the PyTorch sampler `run()` raise.
+Training raises.  `run()` (cuda_ray=False, what `validate.py -O` selects) is the reference's hierarchical sampler on the device,
+with our kernels for near/far and every network query; it is a convenience for callers of that flag, not the benchmarked path.
 """
 import ctypes as C
 import math
@@ -103,9 +104,86 @@ class NeRFRenderer(nn.Module):
         self.mean_count = 0
         self.local_step = 0
 
+    @staticmethod
+    def _sample_pdf(bins, weights, n_samples, det):
+        """nerf/renderer.py:12-46: inverse-CDF resampling.  bins [B,T], weights [B,T-1] -> [B,n_samples]."""
+        weights = weights + 1e-5
+        cdf = torch.cumsum(weights / torch.sum(weights, -1, keepdim=True), -1)
+        cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], -1)
+        shape = list(cdf.shape[:-1]) + [n_samples]
+        if det:
+            u = torch.linspace(0.5 / n_samples, 1.0 - 0.5 / n_samples, steps=n_samples, device=cdf.device, dtype=cdf.dtype).expand(shape)
+        else:
+            u = torch.rand(shape, device=cdf.device, dtype=cdf.dtype)
+        u = u.contiguous()
+        inds = torch.searchsorted(cdf, u, right=True)
+        lo, hi = torch.clamp(inds - 1, min=0), torch.clamp(inds, max=cdf.shape[-1] - 1)
+        cdf_lo, cdf_hi = torch.gather(cdf, 1, lo), torch.gather(cdf, 1, hi)
+        bin_lo, bin_hi = torch.gather(bins, 1, lo), torch.gather(bins, 1, hi)
+        denom = cdf_hi - cdf_lo
+        denom = torch.where(denom < 1e-5, torch.ones_like(denom), denom)
+        return bin_lo + (u - cdf_lo) / denom * (bin_hi - bin_lo)
+
+    def _sample_weights(self, z, sigma, sample_dist):
+        """renderer.py:184-189 == :222-226: alpha from sigma * delta, transmittance by cumprod."""
+        deltas = torch.cat([z[..., 1:] - z[..., :-1], sample_dist * torch.ones_like(z[..., :1])], dim=-1)
+        alphas = 1 - torch.exp(-deltas * self.density_scale * sigma)
+        shifted = torch.cat([torch.ones_like(alphas[..., :1]), 1 - alphas + 1e-15], dim=-1)
+        return alphas * torch.cumprod(shifted, dim=-1)[..., :-1]
+
     def run(self, rays_o, rays_d, num_steps=128, upsample_steps=128, bg_color=None, perturb=False, **kwargs):
-        raise NotImplementedError("NeRFRenderer.run (cuda_ray=False PyTorch sampler, renderer.py:125-258) is the reference's "
-                                  "CPU-baseline path, not part of the B200 hot path; construct the model with cuda_ray=True")
+        """nerf/renderer.py:125-258 -- the `cuda_ray=False` hierarchical sampler (what `validate.py -O` selects), on the DEVICE:
+        near/far, every density query (ngp_density_forward) and every colour query (SH + FFMLP ops) are our kernels; torch
+        only does the sampler's bookkeeping (cumprod / searchsorted / sort / gather) on device tensors.  Same result dict as the
+        reference, including `aggregated_density`.  Inference only; no CPU path (CPU rays are an error)."""
+        if self.training:
+            raise NotImplementedError("run: only the inference branch is built (model.eval())")
+        if self.bg_radius > 0:
+            raise NotImplementedError("run: bg_radius > 0 (background network) is not on the validate.py path (bg_radius=-1)")
+        _cabi.require_cuda(rays_o, rays_d)
+        prefix = rays_o.shape[:-1]
+        rays_o = rays_o.contiguous().view(-1, 3).float()
+        rays_d = rays_d.contiguous().view(-1, 3).float()
+        N = rays_o.shape[0]
+        device = rays_o.device
+        aabb = self.aabb_infer
+        with torch.no_grad():
+            nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, aabb, self.min_near)
+            nears, fars = nears.unsqueeze(-1), fars.unsqueeze(-1)
+            z = nears + (fars - nears) * torch.linspace(0.0, 1.0, num_steps, device=device).unsqueeze(0).expand(N, num_steps)
+            sample_dist = (fars - nears) / num_steps
+            if perturb:
+                z = z + (torch.rand(z.shape, device=device) - 0.5) * sample_dist
+            xyz = torch.min(torch.max(rays_o.unsqueeze(-2) + rays_d.unsqueeze(-2) * z.unsqueeze(-1), aabb[:3]), aabb[3:])
+            dens = {k: v.reshape(N, num_steps, -1) for k, v in self.density(xyz.reshape(-1, 3)).items()}
+            if upsample_steps > 0:
+                sigma = dens["sigma"].squeeze(-1).float()
+                w = self._sample_weights(z, sigma, sample_dist)
+                deltas = z[..., 1:] - z[..., :-1]
+                new_z = self._sample_pdf(z[..., :-1] + 0.5 * deltas, w[:, 1:-1], upsample_steps, det=not self.training)
+                new_xyz = torch.min(torch.max(rays_o.unsqueeze(-2) + rays_d.unsqueeze(-2) * new_z.unsqueeze(-1), aabb[:3]), aabb[3:])
+                new_dens = {k: v.reshape(N, upsample_steps, -1) for k, v in self.density(new_xyz.reshape(-1, 3)).items()}
+                z, order = torch.sort(torch.cat([z, new_z], dim=1), dim=1)
+                xyz = torch.gather(torch.cat([xyz, new_xyz], dim=1), 1, order.unsqueeze(-1).expand(-1, -1, 3))
+                for k in dens:
+                    both = torch.cat([dens[k], new_dens[k]], dim=1)
+                    dens[k] = torch.gather(both, 1, order.unsqueeze(-1).expand_as(both))
+            sigma = dens["sigma"].squeeze(-1).float()
+            w = self._sample_weights(z, sigma, sample_dist)
+            T = z.shape[1]
+            dirs = rays_d.view(-1, 1, 3).expand(N, T, 3)
+            flat = {k: v.reshape(N * T, v.shape[-1]) for k, v in dens.items()}
+            mask = w > 1e-4                                                       # renderer.py:232 "hard coded"
+            rgbs = self.color(xyz.reshape(-1, 3), dirs.reshape(-1, 3), mask=mask.reshape(-1), **flat).view(N, T, 3).float()
+            weights_sum = w.sum(dim=-1)
+            depth = torch.sum(w * ((z - nears) / (fars - nears)).clamp(0, 1), dim=-1)
+            image = torch.sum(w.unsqueeze(-1) * rgbs, dim=-2)
+            if bg_color is None:
+                bg_color = 1
+            image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
+            aggregated_density = torch.sum(w * sigma, dim=1)
+        return {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum, "rgbs": rgbs,
+                "sigmas": flat["sigma"], "aggregated_density": aggregated_density.view(*prefix)}
 
     # ------------------------------------------------------------------ fused-path plumbing (subclass provides the network)
     def _configure_native(self, ctx):
@@ -197,10 +275,26 @@ class NeRFRenderer(nn.Module):
                 "weights_sum": weights_sum}
 
     def render(self, rays_o, rays_d, staged=False, max_ray_batch=4096, **kwargs):
-        """nerf/renderer.py:549-588.  cuda_ray never stages; everything goes to run_cuda in one call."""
-        if not self.cuda_ray:
+        """nerf/renderer.py:549-588.  cuda_ray never stages: everything goes to run_cuda in one call.  cuda_ray=False runs the
+        sampler `run()`, in chunks of max_ray_batch rays per batch element when staged."""
+        if self.cuda_ray:
+            return self.run_cuda(rays_o, rays_d, **kwargs)
+        if not staged:
             return self.run(rays_o, rays_d, **kwargs)
-        return self.run_cuda(rays_o, rays_d, **kwargs)
+        B, N = rays_o.shape[:2]
+        device = rays_o.device
+        depth = torch.empty((B, N), device=device)
+        image = torch.empty((B, N, 3), device=device)
+        aggregated_density = torch.empty((B, N), device=device)
+        part = None
+        for b in range(B):
+            for head in range(0, N, max_ray_batch):
+                tail = min(head + max_ray_batch, N)
+                part = self.run(rays_o[b:b + 1, head:tail], rays_d[b:b + 1, head:tail], **kwargs)
+                depth[b:b + 1, head:tail] = part["depth"]
+                image[b:b + 1, head:tail] = part["image"]
+                aggregated_density[b:b + 1, head:tail] = part["aggregated_density"]
+        return {"depth": depth, "image": image, "rgbs": part["rgbs"], "sigmas": part["sigmas"], "aggregated_density": aggregated_density}
 
     @torch.no_grad()
     def render_poses(self, poses, intrinsics, H, W, **kwargs):

@@ -391,6 +391,17 @@ static_assert(kRenderThreads % 128 == 0 && kRenderGroups <= 8, "the renderer is 
 // 16-byte chunks of a warpgroup's A tile: 8 of hidden activations (+ 4 of encoding staging; with 8 the staging aliases the first
 // four activation chunks, which are idle between the last layer of one pass and the first epilogue of the next)
 constexpr int kTileChunks = NGP_TILE_CHUNKS;
+// A/B switches (tools/ab_build.sh).  NGP_MIN_KSHIFT = 1 (K >= 2: 16 SH rows per warp) with NGP_COARSE_SMEM = 0 (coarse occupancy
+// read from global / L1) brings the CTA under the 132 KB carve-out (124 KB of L1 instead of 92); measured 12.8 ms vs 12.55 ms for
+// the defaults below -- the half-empty passes of the first epoch and the extra spills cost more than the L1 buys.
+#ifndef NGP_MIN_KSHIFT
+#define NGP_MIN_KSHIFT 0
+#endif
+#ifndef NGP_COARSE_SMEM
+#define NGP_COARSE_SMEM 1
+#endif
+constexpr uint32_t kMinKShift = NGP_MIN_KSHIFT;
+constexpr int kShRows = 32 >> NGP_MIN_KSHIFT;   // SH rows (16 halves each) per warp
 constexpr int kMaxStep = 8;                    // renderer.py:357
 constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
 constexpr int kMaxSamplesPerEpoch = 128;      // E * s cap: bounds the longest tile of an epoch
@@ -682,19 +693,21 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     __shared__ __align__(8) uint64_t s_mbar[kRenderGroups], s_aready[kRenderGroups];
     __shared__ GroupSmem s_group[kRenderGroups];
     __shared__ uint32_t s_tmem;
-    // dynamic shared memory: [tcgen05 weights][A tiles, 16 KB per warpgroup][SH rows, 1 KB per warp][coarse occupancy]
+    // dynamic shared memory: [tcgen05 weights][A tiles, 16 KB per warpgroup][SH rows, 32 B x kShRows per warp][coarse occupancy, optional]
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
     uint4 *s_a = s_w + nc.wtc_bytes / 16;
     __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * kTileChunks * tc::kRows);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, wg = warp >> 2, wg_tid = tid & 127;
-    uint32_t *s_coarse = ra.coarse ? reinterpret_cast<uint32_t *>(s_sh_all + (size_t)kRenderWarps * 32 * 16) : nullptr;
+    // coarse occupancy: a shared-memory copy (NGP_COARSE_SMEM) or the global array itself (4 KB, stays in L1)
+    const bool coarse_in_smem = NGP_COARSE_SMEM != 0 && ra.coarse != nullptr;
+    uint32_t *s_coarse = coarse_in_smem ? reinterpret_cast<uint32_t *>(s_sh_all + (size_t)kRenderWarps * kShRows * 16) : const_cast<uint32_t *>(ra.coarse);
     const uint32_t N = ra.N;
     const uint32_t lt_mask = (1u << lane) - 1u;
     long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const long long k_start = kProf ? clock64() : 0;
     for (uint32_t i = tid; i < nc.wtc_bytes / 16; i += blockDim.x) s_w[i] = __ldg(nc.wtc + i);
     tc::fence_async_smem();
-    if (s_coarse)
+    if (coarse_in_smem)
         for (uint32_t i = tid; i < ra.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(ra.coarse + i);
     if (tid < kMaxEpoch) s_hist[tid] = 0;
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(&s_tmem), kRenderTmemCols);
@@ -725,7 +738,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     tt.tmem = tmem_base + (uint32_t)wg * tc::kTmemColsPerTile + ((uint32_t)((warp & 3) * 32) << 16);
     tt.bar_id = 1u + (uint32_t)wg;
     tt.parity = 0;
-    __half *s_sh = s_sh_all + (size_t)warp * 32 * 16;
+    __half *s_sh = s_sh_all + (size_t)warp * kShRows * 16;
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
@@ -770,12 +783,14 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         for (;;) {   // tile geometry; shrink the epoch until its samples fit the buffer (rarely more than one trip)
             ES = E * s;
             tg.kshift = ra.force_kshift < 4u ? ra.force_kshift : (ES >= 5u ? 3u : (ES >= 3u ? 2u : ES - 1u));   // K = 8, 4, 2, 1
+            if (tg.kshift < kMinKShift) tg.kshift = kMinKShift;
             tg.ESp = (ES + (1u << tg.kshift) - 1u) & ~((1u << tg.kshift) - 1u);
             const uint32_t R = 32u >> tg.kshift;
             unsigned long long rows = (unsigned long long)((n_alive + R - 1) / R) * R * tg.ESp;
             if (rows <= ra.cap_rows) break;
             if (E > 1) { E = E > 8u ? E - 8u : E - 1u; continue; }
-            tg.kshift = 0; tg.ESp = ES;   // one iteration, no padding: (n_alive + 31) * s <= N + 248 rows always fits
+            tg.kshift = kMinKShift;       // one iteration, minimal padding: (n_alive + 31) * (s + 1) <= 2 N + 279 rows always fits
+            tg.ESp = (ES + (1u << tg.kshift) - 1u) & ~((1u << tg.kshift) - 1u);
             break;
         }
         EpochCtr *ec = &ra.ctr->e[attempt % 3];
@@ -933,7 +948,7 @@ struct ngp_ctx {
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * kTileChunks * tc::kRows * 16 + (size_t)kRenderWarps * 32 * 32 + NGP_EXTRA_SMEM; }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * kTileChunks * tc::kRows * 16 + (size_t)kRenderWarps * kShRows * 32 + NGP_EXTRA_SMEM; }
 
 extern "C" {
 
@@ -1133,10 +1148,10 @@ static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     // sample buffer of one epoch: rows_per_ray * N rows of 20 B (streamed, evict-first); >= N + 256 rows always fits one iteration
     static const char *rpr_env = getenv("NGP_ROWS_PER_RAY");
     unsigned long long rpr = rpr_env ? strtoull(rpr_env, nullptr, 10) : 32ull;
-    if (rpr < 2) rpr = 2;
+    if (rpr < 3) rpr = 3;
     unsigned long long rows = rpr * cap + 1024;
     if (rows > 0x7fffffffull) rows = 0x7fffffffull;
-    NGP_REQUIRE(rows >= (unsigned long long)N + 256, "render: %u rays do not fit the sample buffer", N);
+    NGP_REQUIRE(rows >= 2ull * N + 512, "render: %u rays do not fit the sample buffer", N);
     NGP_CUDA(cudaMalloc(&c->nears, sizeof(float) * cap));
     NGP_CUDA(cudaMalloc(&c->fars, sizeof(float) * cap));
     NGP_CUDA(cudaMalloc(&c->state[0], sizeof(float4) * 2 * (size_t)cap));
@@ -1175,12 +1190,12 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.coarse = nullptr; ra.coarse_words = 0;
     size_t smem = c->render_smem;
     static const bool no_coarse = getenv("NGP_NO_COARSE") != nullptr;   // A/B switch for profiling only
-    if (!no_coarse && c->coarse_words && smem + c->coarse_words * 4 <= c->render_smem_max) {
+    if (!no_coarse && c->coarse_words && smem + (NGP_COARSE_SMEM ? c->coarse_words * 4 : 0) <= c->render_smem_max) {
         const uint32_t n_blocks = c->coarse_words * 32;
         k_coarse_occupancy<<<div_up(n_blocks, 256), 256, 0, st>>>(reinterpret_cast<const unsigned long long *>(c->bitfield), n_blocks, c->coarse);
         if (int rc = after_launch("coarse_occupancy")) return rc;
         ra.coarse = c->coarse; ra.coarse_words = c->coarse_words;
-        smem += c->coarse_words * 4;
+        if (NGP_COARSE_SMEM) smem += c->coarse_words * 4;
     }
     NetConst nc = c->nc;
     void *args[] = {&nc, &ra};

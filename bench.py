@@ -315,6 +315,7 @@ def main():
     torch.cuda.synchronize()
     stats = out["stats"].cpu().tolist()
     iters, samples = int(stats[0]), int(stats[1])
+    epochs, replays = int(stats[2]), int(stats[3])
     for _ in range(max(args.warmup, 3)):
         flush.zero_()
         render_dev()
@@ -362,7 +363,8 @@ def main():
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
                 "config": {"workload": wl["desc"], "variant": args.variant, "rays_per_gpu_per_step": N, "samples_per_step": samples,
-                           "samples_per_ray": samples / N, "iterations_per_step": iters, "frames_per_step": n_frames,
+                           "samples_per_ray": samples / N, "iterations_per_step": iters, "epochs_per_step": epochs, "replayed_epochs": replays,
+                           "frames_per_step": n_frames,
                            "l2": "flushed between steps (256 MB write)", "parallelism": f"replicated weights, {world} ray shards"},
                 "frames_per_s": n_frames * world / (ms_step * 1e-3), "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(o_pin.numel() * 4 + d_pin.numel() * 4),

@@ -439,6 +439,9 @@ struct RenderArgs {
     uint32_t cap_rows;
     uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t force_kshift;   // >= 4: automatic; else log2 of the samples per ray per evaluation pass (profiling A/B)
+    uint32_t t_div;          // once rays die by transmittance: E = margin / (t_div * rate)
+    uint32_t e0_cap;         // cap on E of the first epoch (0 = none): a short probe epoch learns cheaply whether rays die by transmittance
+    uint32_t rate0_div;      // death-rate prior for the first epochs: N / rate0_div deaths per iteration (1 = assume everything may die)
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -754,7 +757,8 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     }
     grid.sync();
 
-    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = N, E = 1, replays = 0, t_deaths = 0;
+    const uint32_t rate0 = N / (ra.rate0_div ? ra.rate0_div : 1u) + 1u;
+    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = rate0, E = 1, replays = 0, t_deaths = 0;
     bool replay = false;
     while (step < ra.max_steps && n_alive > 0) {
         const uint32_t s = clamp_n_step(N, n_alive);                         // renderer.py:357
@@ -765,10 +769,11 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
                 const uint32_t rate = last_rate < 1u ? 1u : last_rate;
                 // pre-validation makes over-shooting cheap (only marching is wasted) as long as rays die by running out of samples;
                 // transmittance deaths are only found by the evaluator, so be conservative once they show up
-                const uint32_t e = t_deaths ? margin / (2u * rate) : (margin + margin / 2u) / rate + 1u;
+                const uint32_t e = t_deaths ? margin / (ra.t_div * rate) : (margin + margin / 2u) / rate + 1u;
                 E = e < 1u ? 1u : (e > (uint32_t)kMaxEpoch ? (uint32_t)kMaxEpoch : e);
             }
             if (ra.max_epoch && E > ra.max_epoch) E = ra.max_epoch;
+            if (iter == 0 && ra.e0_cap && E > ra.e0_cap) E = ra.e0_cap;
         }
         {
             const uint32_t left = (ra.max_steps - step + s - 1) / s;         // iterations the `while step < max_steps` loop still allows
@@ -863,7 +868,8 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         replay = false;
         step += ran * s;
         iter += ran;
-        last_rate = last;
+        // the rays that miss the box all die in iteration 0: that burst says nothing about the rate of the iterations after it
+        last_rate = (iter == ran && ran == 1u) ? rate0 : last;
         t_deaths = any_t ? 1u : 0u;
         n_alive = na;
         in ^= 1;
@@ -1185,6 +1191,13 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.max_epoch = me_env ? (uint32_t)strtoul(me_env, nullptr, 10) : 0u;
     static const char *ks_env = getenv("NGP_KSHIFT");
     ra.force_kshift = ks_env ? (uint32_t)strtoul(ks_env, nullptr, 10) : 4u;
+    static const char *td_env = getenv("NGP_T_DIV");
+    ra.t_div = td_env ? (uint32_t)strtoul(td_env, nullptr, 10) : 2u;
+    if (ra.t_div < 1u) ra.t_div = 1u;
+    static const char *e0_env = getenv("NGP_E0_CAP");
+    ra.e0_cap = e0_env ? (uint32_t)strtoul(e0_env, nullptr, 10) : 4u;
+    static const char *r0_env = getenv("NGP_RATE0_DIV");
+    ra.rate0_div = r0_env ? (uint32_t)strtoul(r0_env, nullptr, 10) : 128u;
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;

@@ -411,7 +411,7 @@ struct EpochCtr {
     uint32_t cursor;            // MARCH phase: next unclaimed entry of the live list
     uint32_t ticket;            // EVALUATE phase: next unclaimed 32-ray tile
     uint32_t n_out;             // survivors appended to the next live list
-    uint32_t pad;
+    uint32_t opaque;            // some ray of this epoch ended with weights_sum > 0.9: transmittance deaths are near
     uint32_t hist[kMaxEpoch];   // rays that died in iteration j of the epoch
     uint32_t mhist[kMaxEpoch];  // of those, the ones that ran out of samples -- known to the marcher, before anything is evaluated
 };
@@ -663,6 +663,7 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
                 else survives = true;
             }
             if (dead) atomicAdd(s_hist + death, 1u);
+            else if (a.ws > 0.9f && __ldcg(&ec->opaque) == 0u) atomicExch(&ec->opaque, 1u);   // rare: at most a few writers per epoch
             float4 *so = state_out + 2 * (size_t)index;
             __stcg(so, make_float4(a.t, a.ws, a.d, __uint_as_float(seq)));
             __stcg(so + 1, make_float4(a.r, a.g, a.b, __uint_as_float(samples)));
@@ -870,7 +871,8 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         iter += ran;
         // the rays that miss the box all die in iteration 0: that burst says nothing about the rate of the iterations after it
         last_rate = (iter == ran && ran == 1u) ? rate0 : last;
-        t_deaths = any_t ? 1u : 0u;
+        // be conservative as soon as rays die by transmittance -- or are about to (a ray has lost 90 % of its light)
+        t_deaths = (any_t || __ldcg(&ec->opaque) != 0u) ? 1u : 0u;
         n_alive = na;
         in ^= 1;
     }

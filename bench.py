@@ -49,7 +49,7 @@ WORKLOADS = {
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch from the committed `ncu --set full` capture
 # (profiles/r01*_k_render_ncu_summary.txt); None where no capture exists
-NCU_DRAM_BYTES_PER_LAUNCH = {"cfg2": 2749021000}   # profiles/r01m_k_render_ncu_summary.txt: 1.351 GB read + 1.398 GB written (the epoch sample buffer spills past L2)
+NCU_DRAM_BYTES_PER_LAUNCH = {"cfg2": 2834868000}   # profiles/r01n_k_render_ncu_summary.txt: 1.396 GB read + 1.439 GB written (the epoch sample buffer spills past L2)
 
 
 def measured_gather_peak():

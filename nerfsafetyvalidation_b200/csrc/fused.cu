@@ -404,7 +404,10 @@ constexpr uint32_t kMinKShift = NGP_MIN_KSHIFT;
 constexpr int kShRows = 32 >> NGP_MIN_KSHIFT;   // SH rows (16 halves each) per warp
 constexpr int kMaxStep = 8;                    // renderer.py:357
 constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
-constexpr int kMaxSamplesPerEpoch = 128;      // E * s cap: bounds the longest tile of an epoch
+#ifndef NGP_MAX_SAMPLES_PER_EPOCH
+#define NGP_MAX_SAMPLES_PER_EPOCH 128
+#endif
+constexpr int kMaxSamplesPerEpoch = NGP_MAX_SAMPLES_PER_EPOCH;      // E * s cap: bounds the longest tile of an epoch
 constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
 
 struct EpochCtr {

@@ -443,6 +443,7 @@ struct RenderArgs {
     uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t force_kshift;   // >= 4: automatic; else log2 of the samples per ray per evaluation pass (profiling A/B)
     uint32_t t_div;          // once rays die by transmittance: E = margin / (t_div * rate)
+    uint32_t t_cap;          // E * s cap once rays die by transmittance and n_step can still change: bounds what a replay throws away
     uint32_t e0_cap;         // cap on E of the first epoch (0 = none): a short probe epoch learns cheaply whether rays die by transmittance
     uint32_t rate0_div;      // death-rate prior for the first epochs: N / rate0_div deaths per iteration (1 = assume everything may die)
     RenderCtr *ctr;
@@ -782,7 +783,8 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         {
             const uint32_t left = (ra.max_steps - step + s - 1) / s;         // iterations the `while step < max_steps` loop still allows
             if (E > left) E = left;
-            const uint32_t cap = (uint32_t)kMaxSamplesPerEpoch / s;         // bounds the longest tile (load balance)
+            const uint32_t spe = (t_deaths && s < (uint32_t)kMaxStep && ra.t_cap) ? ra.t_cap : (uint32_t)kMaxSamplesPerEpoch;
+            const uint32_t cap = spe / s;                                    // bounds the longest tile (load balance) and the cost of a replay
             if (E > cap) E = cap < 1u ? 1u : cap;
             const uint32_t g = s == 8 ? 1u : (s == 4 ? 2u : (s == 2 || s == 6 ? 4u : 8u));   // E * s a multiple of 8 once it can be
             if (E >= g) E -= E % g;
@@ -1199,6 +1201,8 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     static const char *td_env = getenv("NGP_T_DIV");
     ra.t_div = td_env ? (uint32_t)strtoul(td_env, nullptr, 10) : 2u;
     if (ra.t_div < 1u) ra.t_div = 1u;
+    static const char *tc_env = getenv("NGP_T_CAP");
+    ra.t_cap = tc_env ? (uint32_t)strtoul(tc_env, nullptr, 10) : 16u;
     static const char *e0_env = getenv("NGP_E0_CAP");
     ra.e0_cap = e0_env ? (uint32_t)strtoul(e0_env, nullptr, 10) : 4u;
     static const char *r0_env = getenv("NGP_RATE0_DIV");

@@ -1,7 +1,7 @@
-for g in 0 3 6; do
-for args in "--workload cfg2" "--workload cfg2 --variant B" "--workload rollout --variant B"; do
-    NGP_E_GROW=$g timeout 300 python bench.py $args --steps 10 --warmup 3 --no-cpu-baseline --no-ref-gpu > gpurun_out/r0.json 2> gpurun_out/r0.err
+for g in 8 16 24; do
+for args in "--workload cfg2 --variant B" "--workload rollout --variant B" "--workload cfg2"; do
+    NGP_T_CAP=$g timeout 300 python bench.py $args --steps 8 --warmup 3 --no-cpu-baseline --no-ref-gpu > gpurun_out/r0.json 2> gpurun_out/r0.err
     python -c "
-import json; d=json.load(open('gpurun_out/r0.json')); c=d['config']; print('GROW $g', '$args', '| ms', round(d['ms_per_step'],3), 'iters', c['iterations_per_step'], 'epochs', c['epochs_per_step'], 'replays', c['replayed_epochs'])"
+import json; d=json.load(open('gpurun_out/r0.json')); c=d['config']; print('TCAP $g', '$args', '| ms', round(d['ms_per_step'],3), 'iters', c['iterations_per_step'], 'epochs', c['epochs_per_step'], 'replays', c['replayed_epochs'])"
 done
 done

@@ -79,18 +79,23 @@ def parse():
     return p.parse_args()
 
 
-def frame_rays(wl, rank, n_frames=1):
+def frame_rays(wl, rank, n_frames=1, with_poses=False):
     """rays of rank `rank`'s step.  Single frames: cameras on the cfg2 orbit, azimuth advanced per rank.  Rollout batches
     (cfg3): the first n_frames frames of this rank's disturbance rollouts (rollouts.py: drone dynamics + per-rollout seeded
-    noise + the simulator's pose conversion), i.e. what NerfSimulator would hand to render() during a Monte Carlo run."""
+    noise + the simulator's pose conversion), i.e. what NerfSimulator would hand to render() during a Monte Carlo run.
+    with_poses: also return the [F,4,4] cam2world poses the rays were generated from."""
     from nerfsafetyvalidation_b200 import rollouts as ro, synthetic as syn
     if n_frames > 1:
         steps = wl.get("rollout_steps", 20)
         ids = ro.shard_ids(10 ** 6, rank, max(int(os.environ.get("WORLD_SIZE", "1")), 1))[: -(-n_frames // steps)]
-        o, d, _, _ = ro.rollout_rays(ids, steps, wl["H"], wl["W"], wl["focal"])
-        return np.ascontiguousarray(o[:n_frames].reshape(-1, 3)), np.ascontiguousarray(d[:n_frames].reshape(-1, 3))
-    o, d = syn.pinhole_rays(syn.orbit_pose(37.0 + 45.0 * rank), wl["H"], wl["W"], focal=wl["focal"])
-    return o, d
+        o, d, states, _ = ro.rollout_rays(ids, steps, wl["H"], wl["W"], wl["focal"])
+        o, d = np.ascontiguousarray(o[:n_frames].reshape(-1, 3)), np.ascontiguousarray(d[:n_frames].reshape(-1, 3))
+        poses = np.ascontiguousarray(ro.states_to_ngp_poses(states.reshape(-1, 12))[:n_frames], np.float32)
+    else:
+        pose = syn.orbit_pose(37.0 + 45.0 * rank)
+        o, d = syn.pinhole_rays(pose, wl["H"], wl["W"], focal=wl["focal"])
+        poses = np.asarray(pose, np.float32)[None].copy()
+    return (o, d, poses) if with_poses else (o, d)
 
 
 def scene_for(wl):
@@ -258,7 +263,7 @@ def main():
     lib = _cabi.load()
 
     n_frames = wl.get("frames", 1)
-    o_np, d_np = frame_rays(wl, rank, n_frames)
+    o_np, d_np, poses_np = frame_rays(wl, rank, n_frames, with_poses=True)
     N = o_np.shape[0]
     o_dev, d_dev = torch.from_numpy(o_np).to(dev), torch.from_numpy(d_np).to(dev)
     o_pin, d_pin = torch.from_numpy(o_np).pin_memory(), torch.from_numpy(d_np).pin_memory()
@@ -278,9 +283,8 @@ def main():
         _cabi.check(lib.ngp_render_host(h, _cabi.ptr(o_pin), _cabi.ptr(d_pin), N, 0.0, 1024, 1.0, _cabi.ptr(img_pin), _cabi.ptr(dep_pin),
                                         _cabi.stream()), "ngp_render_host")
 
-    pose_pin = None
-    if n_frames == 1:   # single-camera workloads: the same frame from its 4x4 pose (64 B up instead of 24 B per ray)
-        pose_pin = torch.from_numpy(np.asarray(syn.orbit_pose(37.0 + 45.0 * rank), np.float32)[None].copy()).pin_memory()
+    # the same frames from their 4x4 poses (64 B per frame up instead of 24 B per ray)
+    pose_pin = torch.from_numpy(poses_np).pin_memory()
 
     def render_pose_host():
         model.render_poses_host(pose_pin, (wl["focal"], wl["focal"], wl["W"] / 2, wl["H"] / 2), wl["H"], wl["W"], image=img_pin, depth=dep_pin,
@@ -371,7 +375,7 @@ def main():
                         "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_e2e / args.steps,
                         "api": "ngp_render_host (C ABI, pinned host buffers)"},
                 "e2e_from_pose": None if not ms_pose else {
-                    "value": rays_all / (ms_pose / args.steps * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 64,
+                    "value": rays_all / (ms_pose / args.steps * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(pose_pin.numel() * 4),
                     "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_pose / args.steps,
                     "api": "ngp_render_poses_host (C ABI: host 4x4 pose in, rays generated on the device by ngp_get_rays, host image + depth out)"},
                 "gpu_launches": int(launches),

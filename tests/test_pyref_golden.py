@@ -47,3 +47,16 @@ def test_chunking_does_not_change_the_result():
     a = rs.render(net, torch.from_numpy(o[0]), torch.from_numpy(d[0]), max_ray_batch=4096)
     b = rs.render(net, torch.from_numpy(o[0]), torch.from_numpy(d[0]), max_ray_batch=50)
     assert np.abs(a["image"].numpy() - b["image"].numpy()).max() <= 1e-6
+
+
+def test_bench_poses_reproduce_the_bench_rays():
+    """bench.py hands the same frames to the ray API and to the pose API (e2e_from_pose): the poses must regenerate the rays."""
+    import bench
+    wl = dict(bench.WORKLOADS["rollout"], H=20, W=24, focal=30.0)
+    o, d, poses = bench.frame_rays(wl, 0, 5, with_poses=True)
+    o2, d2 = rs.get_rays(poses, wl["focal"], wl["focal"], wl["W"] / 2, wl["H"] / 2, wl["H"], wl["W"])
+    assert poses.shape == (5, 4, 4) and np.array_equal(o2.reshape(-1, 3), o) and np.abs(d2.reshape(-1, 3) - d).max() <= 2e-7
+    wl = dict(bench.WORKLOADS["cfg2"], H=16, W=16, focal=22.0)
+    o, d, poses = bench.frame_rays(wl, 3, 1, with_poses=True)
+    o2, d2 = rs.get_rays(poses, 22.0, 22.0, 8.0, 8.0, 16, 16)
+    assert np.array_equal(o2.reshape(-1, 3), o) and np.abs(d2.reshape(-1, 3) - d).max() <= 2e-7

@@ -46,7 +46,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = os.path.join(OBJ, os.path.basename(src)[:-3] + ".ptxas.log")
         with open(log, "w") as f:
-            f.write(r.stderr)
+            f.write("".join(ln for ln in r.stderr.splitlines(True) if "Compile time" not in ln))   # keep the tracked log stable
         if r.returncode != 0:
             sys.stderr.write(r.stderr)
             raise RuntimeError(f"nvcc failed on {src}")

@@ -443,9 +443,12 @@ struct RenderArgs {
     uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t force_kshift;   // >= 4: automatic; else log2 of the samples per ray per evaluation pass (profiling A/B)
     uint32_t t_div;          // once rays die by transmittance: E = margin / (t_div * rate)
-    uint32_t t_cap;          // E * s cap once rays die by transmittance and n_step can still change: bounds what a replay throws away
+    // iterations-per-epoch caps per n_step (index s - 1), host-computed so the device does no division: cap_n = 128 / s bounds the
+    // longest tile; cap_t = 16 / s applies once rays die by transmittance while n_step can still change (s < 8) and bounds what a
+    // replay throws away
+    uint32_t cap_n[kMaxStep], cap_t[kMaxStep];
     uint32_t e0_cap;         // cap on E of the first epoch (0 = none): a short probe epoch learns cheaply whether rays die by transmittance
-    uint32_t rate0_div;      // death-rate prior for the first epochs: N / rate0_div deaths per iteration (1 = assume everything may die)
+    uint32_t rate0;          // death-rate prior for the first epochs: N / 128 + 1 deaths per iteration (NGP_RATE0_DIV overrides the 128)
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -762,8 +765,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     }
     grid.sync();
 
-    const uint32_t rate0 = N / (ra.rate0_div ? ra.rate0_div : 1u) + 1u;
-    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = rate0, E = 1, replays = 0, t_deaths = 0;
+    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = ra.rate0, E = 1, replays = 0, t_deaths = 0;
     bool replay = false;
     while (step < ra.max_steps && n_alive > 0) {
         const uint32_t s = clamp_n_step(N, n_alive);                         // renderer.py:357
@@ -783,9 +785,8 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         {
             const uint32_t left = (ra.max_steps - step + s - 1) / s;         // iterations the `while step < max_steps` loop still allows
             if (E > left) E = left;
-            const uint32_t spe = (t_deaths && s < (uint32_t)kMaxStep && ra.t_cap) ? ra.t_cap : (uint32_t)kMaxSamplesPerEpoch;
-            const uint32_t cap = spe / s;                                    // bounds the longest tile (load balance) and the cost of a replay
-            if (E > cap) E = cap < 1u ? 1u : cap;
+            const uint32_t cap = (t_deaths && s < (uint32_t)kMaxStep) ? ra.cap_t[s - 1u] : ra.cap_n[s - 1u];   // both >= 1
+            if (E > cap) E = cap;
             const uint32_t g = s == 8 ? 1u : (s == 4 ? 2u : (s == 2 || s == 6 ? 4u : 8u));   // E * s a multiple of 8 once it can be
             if (E >= g) E -= E % g;
         }
@@ -875,7 +876,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         step += ran * s;
         iter += ran;
         // the rays that miss the box all die in iteration 0: that burst says nothing about the rate of the iterations after it
-        last_rate = (iter == ran && ran == 1u) ? rate0 : last;
+        last_rate = (iter == ran && ran == 1u) ? ra.rate0 : last;
         // be conservative as soon as rays die by transmittance -- or are about to (a ray has lost 90 % of its light)
         t_deaths = (any_t || __ldcg(&ec->opaque) != 0u) ? 1u : 0u;
         n_alive = na;
@@ -1202,11 +1203,21 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.t_div = td_env ? (uint32_t)strtoul(td_env, nullptr, 10) : 2u;
     if (ra.t_div < 1u) ra.t_div = 1u;
     static const char *tc_env = getenv("NGP_T_CAP");
-    ra.t_cap = tc_env ? (uint32_t)strtoul(tc_env, nullptr, 10) : 16u;
+    {
+        const uint32_t t_cap = tc_env ? (uint32_t)strtoul(tc_env, nullptr, 10) : 16u;
+        for (uint32_t k = 1; k <= (uint32_t)kMaxStep; k++) {
+            const uint32_t n = (uint32_t)kMaxSamplesPerEpoch / k, t = (t_cap ? t_cap : (uint32_t)kMaxSamplesPerEpoch) / k;
+            ra.cap_n[k - 1] = n < 1u ? 1u : n;
+            ra.cap_t[k - 1] = t < 1u ? 1u : t;
+        }
+    }
     static const char *e0_env = getenv("NGP_E0_CAP");
     ra.e0_cap = e0_env ? (uint32_t)strtoul(e0_env, nullptr, 10) : 4u;
     static const char *r0_env = getenv("NGP_RATE0_DIV");
-    ra.rate0_div = r0_env ? (uint32_t)strtoul(r0_env, nullptr, 10) : 128u;
+    {
+        const uint32_t div = r0_env ? (uint32_t)strtoul(r0_env, nullptr, 10) : 128u;
+        ra.rate0 = N / (div ? div : 1u) + 1u;
+    }
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;

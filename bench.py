@@ -200,6 +200,7 @@ def run_reference_arm(args, wl):
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)   # torchrun exports OMP_NUM_THREADS=1; this arm is meant to use every host core
     n = args.cpu_rays or 20000
     vals, secs = [], []
     for i in range(args.warmup + args.steps):

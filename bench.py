@@ -76,6 +76,9 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-ref-gpu", action="store_true")
     p.add_argument("--cpu-rays", type=int, default=0, help="rays in the CPU sample (0 = auto)")
+    p.add_argument("--split-rows", action="store_true",
+                   help="single-frame workloads under torchrun: ONE frame, rank r renders the r-th block of image rows (strong scaling; "
+                        "SURVEY section 8d cfg5) instead of one frame per rank")
     return p.parse_args()
 
 
@@ -264,7 +267,11 @@ def main():
     lib = _cabi.load()
 
     n_frames = wl.get("frames", 1)
-    o_np, d_np, poses_np = frame_rays(wl, rank, n_frames, with_poses=True)
+    split_rows = args.split_rows and world > 1 and n_frames == 1
+    o_np, d_np, poses_np = frame_rays(wl, 0 if split_rows else rank, n_frames, with_poses=True)
+    if split_rows:   # contiguous row blocks keep the live-list order within a rank; the n_step schedule becomes per rank
+        r0, r1 = wl["H"] * rank // world, wl["H"] * (rank + 1) // world
+        o_np, d_np = np.ascontiguousarray(o_np[r0 * wl["W"]:r1 * wl["W"]]), np.ascontiguousarray(d_np[r0 * wl["W"]:r1 * wl["W"]])
     N = o_np.shape[0]
     o_dev, d_dev = torch.from_numpy(o_np).to(dev), torch.from_numpy(d_np).to(dev)
     o_pin, d_pin = torch.from_numpy(o_np).pin_memory(), torch.from_numpy(d_np).pin_memory()
@@ -284,8 +291,8 @@ def main():
         _cabi.check(lib.ngp_render_host(h, _cabi.ptr(o_pin), _cabi.ptr(d_pin), N, 0.0, 1024, 1.0, _cabi.ptr(img_pin), _cabi.ptr(dep_pin),
                                         _cabi.stream()), "ngp_render_host")
 
-    # the same frames from their 4x4 poses (64 B per frame up instead of 24 B per ray)
-    pose_pin = torch.from_numpy(poses_np).pin_memory()
+    # the same frames from their 4x4 poses (64 B per frame up instead of 24 B per ray); a row block has no pose of its own
+    pose_pin = None if split_rows else torch.from_numpy(poses_np).pin_memory()
 
     def render_pose_host():
         model.render_poses_host(pose_pin, (wl["focal"], wl["focal"], wl["W"] / 2, wl["H"] / 2), wl["H"], wl["W"], image=img_pin, depth=dep_pin,
@@ -365,13 +372,13 @@ def main():
         gather_peak = measured_gather_peak()
         ggathers = samples * 128 / (ms_step * 1e-3) / 1e9
         line = {"metric": "rendered Mrays/s (NGP hashgrid, cuda_ray inference)", "value": value, "unit": "Mrays/s", "n_gpus": world,
-                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if split_rows else "weak",
                 "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
                 "config": {"workload": wl["desc"], "variant": args.variant, "rays_per_gpu_per_step": N, "samples_per_step": samples,
                            "samples_per_ray": samples / N, "iterations_per_step": iters, "epochs_per_step": epochs, "replayed_epochs": replays,
                            "frames_per_step": n_frames,
-                           "l2": "flushed between steps (256 MB write)", "parallelism": f"replicated weights, {world} ray shards"},
-                "frames_per_s": n_frames * world / (ms_step * 1e-3), "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
+                           "l2": "flushed between steps (256 MB write)", "parallelism": f"replicated weights, {world} ray shards" + (" (row blocks of ONE frame)" if split_rows else "")},
+                "frames_per_s": n_frames * (1 if split_rows else world) / (ms_step * 1e-3), "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(o_pin.numel() * 4 + d_pin.numel() * 4),
                         "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_e2e / args.steps,
                         "api": "ngp_render_host (C ABI, pinned host buffers)"},

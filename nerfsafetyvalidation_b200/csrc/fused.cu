@@ -1,13 +1,14 @@
 // fused.cu -- the B200 fast path (no upstream counterpart):
-//   ngp_network_forward : hash-grid encode -> sigma MLP -> SH -> colour MLP -> exp/sigmoid, one kernel, nothing but
-//                         xyz/dir in and sigma/rgb out touches HBM        (nerf/network_ff.py:51-74)
+//   ngp_network_forward(_tc) : hash-grid encode -> sigma MLP -> SH -> colour MLP -> exp/sigmoid, one kernel, nothing but
+//                         xyz/dir in and sigma/rgb out touches HBM        (nerf/network_ff.py:51-74); _tc = tcgen05 tiles
+//   ngp_density_forward : the density half of it (nerf/network_ff.py:76-89)
 //   ngp_render          : NeRFRenderer.run_cuda's whole inference loop (nerf/renderer.py:261-284,329-386) as ONE
-//                         persistent cooperative launch, one 16-warp CTA per SM.  Warps are autonomous: a warp pulls a
-//                         group of 32 live rays and, per sample, runs {march_one -> hash-grid gather -> both MLPs on
-//                         tensor cores -> composite} with lane r owning ray r / row r; nothing but o/d in and the ray
-//                         accumulators out touches HBM.  The grid meets once per iteration because the reference's
-//                         `n_step = clamp(N // n_alive, 1, 8)` schedule is global and the per-ray sample counts (an
-//                         integer output we must match) depend on it.
+//                         persistent cooperative launch, one CTA of 5 warpgroups per SM.  The reference's global schedule
+//                         `n_step = clamp(N // n_alive, 1, 8)` decides where every ray's chunks end and is reproduced
+//                         exactly, but in speculative EPOCHS of many reference iterations (two grid barriers per epoch):
+//                         a lane-dynamic lockstep MARCH phase fills a sample buffer, an EVALUATE + COMPOSITE phase walks
+//                         it in 128-row warpgroup tiles (hash-grid gather -> both MLPs on tcgen05 with TMEM accumulators
+//                         -> compositing in registers).  See the comment above k_render and DESIGN.md section 4.1.
 #include <cooperative_groups.h>
 #include <float.h>
 #include <stddef.h>
@@ -369,10 +370,11 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
 //             lockstep with the other 31 lanes of its warp, and the moment its ray has its E*s samples (or left the box) the
 //             lane takes the next live ray from the list.  Samples go to a streaming buffer (20 B per sample, evict-first)
 //             laid out per 32-ray tile as [sample i][ray r] so the evaluator reads it fully coalesced.
-//   EVALUATE  a warp pulls a tile of 32 consecutive live rays (adjacent pixels: their samples share hash-grid cells) and walks
-//   + COMPOSITE  their samples in lockstep, pass i = sample i of each ray: 16-level gather -> sigma MLP -> SH + colour MLP on
-//             tensor cores with the weights resident in shared memory, then lane r composites its sample into the ray
-//             accumulators it holds in registers for the whole epoch (raymarching.cu:828-913), early termination included.
+//   EVALUATE  a WARPGROUP pulls a 128-row tile: each of its 4 warps owns R = 32 / K consecutive live rays (adjacent pixels:
+//   + COMPOSITE  their samples share hash-grid cells) and evaluates K consecutive samples of each per pass: 16-level gather ->
+//             sigma MLP -> SH + colour MLP as tcgen05.mma on the 128 rows (weights resident in shared memory, accumulators in
+//             TMEM, tc_mlp.cuh), then the leader lane of every ray composites its K samples into the ray accumulators it
+//             holds in registers for the whole epoch (raymarching.cu:828-913), early termination included.
 //             Ray state makes one 32-byte round trip per EPOCH; dirs / sigmas / rgbs never exist in memory.
 #ifndef NGP_RENDER_THREADS
 #define NGP_RENDER_THREADS 640

@@ -60,3 +60,17 @@ def test_bench_poses_reproduce_the_bench_rays():
     o, d, poses = bench.frame_rays(wl, 3, 1, with_poses=True)
     o2, d2 = rs.get_rays(poses, 22.0, 22.0, 8.0, 8.0, 16, 16)
     assert np.array_equal(o2.reshape(-1, 3), o) and np.abs(d2.reshape(-1, 3) - d).max() <= 2e-7
+
+
+def test_cfg1_full_frame_reproduces_the_reference_probe():
+    """BASELINE configs[0] at its full size (100x100, 64+64 samples, seed 0): SURVEY.md Appendix C records the mean pixel the
+    reference's own run() produced for it, 0.59923."""
+    import math
+    H = W = 100
+    fl = 0.5 * W / math.tan(0.5 * 0.6911112)
+    pose = np.eye(4, dtype=np.float32)
+    pose[2, 3] = -2.5
+    o, d = rs.get_rays(pose[None], fl, fl, W / 2, H / 2, H, W)
+    out = rs.render(rs.VanillaNeRF(seed=0), torch.from_numpy(o[0]), torch.from_numpy(d[0]), max_ray_batch=4096, num_steps=64,
+                    upsample_steps=64, bg_color=1.0)
+    assert abs(float(out["image"].mean()) - 0.59923) <= 1e-5

@@ -181,11 +181,12 @@ def cem_update(risks_local, noise_local, ids_local, n_rollouts, m_elite, p_mean,
     pad_i[: risks_local.numel()] = torch.as_tensor(ids_local, device=dev)
     all_r = _all_gather_1d(pad_r, world)
     all_i = _all_gather_1d(pad_i, world)
-    # the same total order on every rank: by risk, ties by rollout id (np.argsort in the reference is order-dependent on ties)
-    order = sorted(range(all_r.numel()), key=lambda k: (float(all_r[k]), int(all_i[k])))
-    elite_ids = [int(all_i[k]) for k in order[:m_elite] if int(all_i[k]) >= 0]
-    elite_set = set(elite_ids)
-    mine = torch.tensor([int(i) in elite_set for i in ids_local], dtype=torch.bool, device=dev)
+    # the same total order on every rank: by risk, ties by rollout id (np.argsort in the reference is order-dependent on ties).
+    # ONE device->host copy of the two small vectors, then a host lexsort (no per-element .item() syncs)
+    r_host, i_host = all_r.cpu().numpy(), all_i.cpu().numpy()
+    order = np.lexsort((i_host, r_host))
+    elite_ids = [int(i) for i in i_host[order[:m_elite]] if i >= 0]
+    mine = torch.from_numpy(np.isin(np.asarray(ids_local, np.int64), np.asarray(elite_ids, np.int64))).to(dev)
     x = noise_local.to(dev)[mine].double()                                   # [E_local, steps, 12]
     steps = x.shape[1] if x.ndim == 3 else p_mean.shape[0]
     pm, ps, qm, qs = (torch.as_tensor(np.array(a, dtype=np.float64), device=dev) for a in (p_mean, p_std, q_mean, q_std))
@@ -197,20 +198,39 @@ def cem_update(risks_local, noise_local, ids_local, n_rollouts, m_elite, p_mean,
     mx = lw.max(dim=0).values if lw.numel() else torch.full((steps,), -float("inf"), dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    w = torch.exp(lw - mx)                                                   # unnormalised, <= 1
-    mom = torch.zeros(steps, 26, dtype=torch.float64, device=dev)            # sum w, sum w^2, sum w x [12], sum w x^2 [12]
-    if w.numel():
-        mom[:, 0] = w.sum(0)
-        mom[:, 1] = (w * w).sum(0)
-        mom[:, 2:14] = torch.einsum("es,esk->sk", w, x)
-        mom[:, 14:26] = torch.einsum("es,esk->sk", w, x * x)
-    if world > 1:
-        dist.all_reduce(mom, op=dist.ReduceOp.SUM)
-    sw, sw2 = mom[:, 0:1], mom[:, 1:2]
-    mean = mom[:, 2:14] / sw
-    # torch.cov(aweights=w, correction=1): sum w (x - mean)^2 / (sum w - sum w^2 / sum w)
-    var = (mom[:, 14:26] - sw * mean * mean) / (sw - sw2 / sw)
-    var = torch.clamp(var, 0.0, 0.1)
+    # CrossEntropyMethod.py:225-236: w = exp(lw - logsumexp(lw)); if ANY weight underflowed to <= 0, w = clamp(w, min=1e-8).
+    # With e = exp(lw - max) and S = sum e over all elites, w = e / S, and w <= 0 exactly where e == 0: the first all-reduce
+    # carries S, the moments of e and the global count of underflowed weights.  Only if that count is non-zero (rare) a second
+    # all-reduce redoes the moments with the clamped weights, as the reference would.
+    e = torch.exp(lw - mx)                                                   # unnormalised, <= 1
+
+    def moments(wt, extra=None):   # sum w, sum w^2, sum w x [12], sum w x^2 [12] (, extra)
+        m = torch.zeros(steps, 27, dtype=torch.float64, device=dev)
+        if wt.numel():
+            m[:, 0] = wt.sum(0)
+            m[:, 1] = (wt * wt).sum(0)
+            m[:, 2:14] = torch.einsum("es,esk->sk", wt, x)
+            m[:, 14:26] = torch.einsum("es,esk->sk", wt, x * x)
+            if extra is not None:
+                m[:, 26] = extra.sum(0)
+        if world > 1:
+            dist.all_reduce(m, op=dist.ReduceOp.SUM)
+        return m
+
+    mom = moments(e, (e <= 0).double())
+    S = mom[:, 0:1]
+    if bool((mom[:, 26] > 0).any()):                                         # identical on every rank (all-reduced)
+        mom = moments(torch.clamp(e / S.t(), min=1e-8))
+        sw, sw2, swx, swx2 = mom[:, 0:1], mom[:, 1:2], mom[:, 2:14], mom[:, 14:26]
+    else:
+        sw, sw2, swx, swx2 = S / S, mom[:, 1:2] / (S * S), mom[:, 2:14] / S, mom[:, 14:26] / S
+    mean = swx                                                               # :238  mean = weights @ samples (weights as clamped, not renormalised)
+    avg = swx / sw                                                           # torch.cov normalises its aweights itself
+    # torch.cov(aweights=w, correction=1): sum w (x - avg)^2 / (sum w - sum w^2 / sum w)
+    denom = sw - sw2 / sw
+    var = (swx2 - sw * avg * avg) / torch.where(denom > 0, denom, torch.full_like(denom, float("nan")))
+    var = torch.nan_to_num(var, nan=0.0, posinf=0.1, neginf=0.0)             # one elite carrying all the weight: torch.cov gives nan/inf; the proposal keeps a zero width there
+    var = torch.clamp(var, 0.0, 0.1)                                         # :243-245
     return mean, var, elite_ids
 
 

@@ -158,8 +158,10 @@ class RefModel:
         return sigma, rgb
 
     @torch.no_grad()
-    def run_cuda(self, rays_o, rays_d, dt_gamma=0, bg_color=1, max_steps=1024, record=None):
-        """renderer.py:261-284,329-386.  `record`: optional list receiving per-iteration snapshots (teacher forcing)."""
+    def run_cuda(self, rays_o, rays_d, dt_gamma=0, bg_color=1, max_steps=1024, record=None, count=True):
+        """renderer.py:261-284,329-386.  `record`: optional list receiving per-iteration snapshots (teacher forcing).
+        `count=False` runs the loop exactly as the reference does (no per-ray sample counting, no extra host sync): the form
+        bench.py times as `reference_gpu`."""
         rays_o = rays_o.contiguous().view(-1, 3)
         rays_d = rays_d.contiguous().view(-1, 3)
         N = rays_o.shape[0]
@@ -173,6 +175,7 @@ class RefModel:
         rays_alive = torch.arange(n_alive, dtype=torch.int32, device=device)
         rays_t = nears.clone()
         step = iters = samples = 0
+        sigmas = rgbs = None
         while step < max_steps:
             n_alive = rays_alive.shape[0]
             if n_alive <= 0:
@@ -186,9 +189,10 @@ class RefModel:
                 record.append(dict(n_alive=n_alive, n_step=n_step, rays_alive=rays_alive.clone(), rays_t=rays_t.clone(),
                                    xyzs=xyzs, dirs=dirs, deltas=deltas, sigmas=sigmas.clone(), rgbs=rgbs.clone(),
                                    weights_sum=weights_sum.clone(), depth=depth.clone(), image=image.clone()))
-            cnt = (deltas[: n_alive * n_step, 0] != 0).view(n_alive, n_step).sum(1).int()
-            spr.index_add_(0, rays_alive.long(), cnt)
-            samples += int(cnt.sum().item())
+            if count:
+                cnt = (deltas[: n_alive * n_step, 0] != 0).view(n_alive, n_step).sum(1).int()
+                spr.index_add_(0, rays_alive.long(), cnt)
+                samples += int(cnt.sum().item())
             composite_rays(n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image)
             if record is not None:
                 record[-1].update(alive_after=rays_alive.clone(), rays_t_after=rays_t.clone(), weights_sum_after=weights_sum.clone(),
@@ -198,5 +202,5 @@ class RefModel:
             iters += 1
         image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
         depth = torch.clamp(depth - nears, min=0) / (fars - nears)
-        return dict(image=image, depth=depth, weights_sum=weights_sum, samples_per_ray=spr, iterations=iters, samples=samples,
-                    nears=nears, fars=fars)
+        return dict(image=image, depth=depth, weights_sum=weights_sum, samples_per_ray=spr if count else None, iterations=iters,
+                    samples=samples if count else None, nears=nears, fars=fars, sigmas=sigmas, rgbs=rgbs)

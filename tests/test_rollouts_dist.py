@@ -96,6 +96,8 @@ def cem_reference(risks, noise, m_elite, pm, ps, qm, qs):
         q = MVN(torch.tensor(qm[i]), torch.diag(torch.tensor(qs[i]) ** 2))
         lw = p.log_prob(es[:, i]) - q.log_prob(es[:, i])
         w = torch.exp(lw - torch.logsumexp(lw, 0))
+        if torch.any(w <= 0):                      # CrossEntropyMethod.py:233-236
+            w = torch.clamp(w, min=1e-8)
         means.append(w @ es[:, i])
         variances.append(torch.clamp(torch.cov(es[:, i].T, aweights=w).diag(), 0, 0.1))
     return torch.stack(means), torch.stack(variances), idx
@@ -119,6 +121,21 @@ def test_cem_update_single_process():
     assert sorted(elite) == sorted(ridx.tolist())
     assert torch.allclose(mean, rm, atol=1e-12) and torch.allclose(var, rv, atol=1e-12)
     assert (var >= 0).all() and (var <= 0.1).all()
+
+
+def test_cem_update_with_one_dominant_elite():
+    """A proposal far narrower than the nominal model makes the importance weights of all elites but a few underflow to exactly 0:
+    the reference then clamps ALL weights to >= 1e-8 (CrossEntropyMethod.py:233-236).  The update must stay finite and equal to it."""
+    n, m = 64, 8
+    noise, risks, pm, ps, qm, qs = cem_inputs(n)
+    qs = ps * 0.01                                  # log q ~ -(x / (0.01 std))^2 / 2: differences of thousands between elites
+    rm, rv, ridx = cem_reference(risks, noise, m, pm, ps, qm, qs)
+    lw_span = []
+    mean, var, elite = ro.cem_update(risks, noise, np.arange(n), n, m, pm, ps, qm, qs)
+    assert torch.isfinite(mean).all() and torch.isfinite(var).all() and (var >= 0).all() and (var <= 0.1).all()
+    assert sorted(elite) == sorted(ridx.tolist())
+    assert torch.allclose(mean, rm, atol=1e-12)
+    assert torch.allclose(var, torch.nan_to_num(rv, nan=0.0, posinf=0.1, neginf=0.0), atol=1e-12)
 
 
 def _free_port():

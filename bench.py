@@ -263,7 +263,7 @@ def main():
     if world > 1:
         for t in (model.encoder.embeddings.data, model.sigma_net.weights.data, model.color_net.weights.data, model.density_bitfield):
             dist.broadcast(t, src=0)
-        model.encoder._half = model.sigma_net._half = model.color_net._half = None
+        model.invalidate_caches()
     lib = _cabi.load()
 
     n_frames = wl.get("frames", 1)
@@ -328,6 +328,7 @@ def main():
     stats = out["stats"].cpu().tolist()
     iters, samples = int(stats[0]), int(stats[1])
     epochs, replays = int(stats[2]), int(stats[3])
+    assert epochs >= 0, "ngp_render: the kernel's schedule check failed (stats[2] = -1)"
     for _ in range(max(args.warmup, 3)):
         flush.zero_()
         render_dev()

@@ -115,10 +115,18 @@ int ngp_ctx_set_network(ngp_ctx *ctx, const void *table_f16, const int32_t *offs
 /* nerf/renderer.py:73-99 state: bitfield [cascade*grid^3/8] bytes (borrowed), aabb = HOST float[6]. */
 int ngp_ctx_set_scene(ngp_ctx *ctx, const uint8_t *bitfield, uint32_t cascade, uint32_t grid_size,
                       const float *aabb_host, float min_near);
+/* Tunables of ngp_render's epoch policy, per context (the library keeps no process-wide state and reads no environment
+ * variables; no upstream counterpart).  name: "rows_per_ray" (sample-buffer rows per ray, default 32), "max_epoch" (cap on the
+ * reference iterations per epoch, 0 = none; 1 = one barrier pair per reference iteration), "kshift" (log2 samples per ray per
+ * pass, >= 4 = automatic), "t_div", "t_cap", "e0_cap", "rate0_div" (epoch-length policy),
+ * "no_coarse" (1 = march without the coarse occupancy grid).  No option changes any output.  Unknown names are an error. */
+int ngp_ctx_set_option(ngp_ctx *ctx, const char *name, uint64_t value);
 /* Diagnostics for the persistent renderer (no upstream counterpart): when enabled, every warp of ngp_render accumulates
  * clock64() cycles per phase.  ngp_ctx_phase_cycles synchronises the device and copies the 8 sums to HOST memory:
- * {0 refill/bookkeeping/prologue/epilogue, 1 march, 2 row packing, 3 hash-grid gather, 4 MLPs, 5 composite, 6 grid barrier,
- *  7 total}, each summed over all warps of all launches since the last reset. */
+ * {0 tile set-up / tile end + prologue / epilogue / loop control, 1 march, 2 grid barrier after march, 3 gather warps: sample
+ *  load + hash-grid gather + operand store, 4 epilogue warps: activations + compositing, 5 gather warps waiting (operand slot,
+ *  accumulators), 6 epilogue warps waiting (layer commits), 7 grid barrier after evaluate}, each summed over all warps of all
+ * launches since the last reset. */
 int ngp_ctx_enable_profile(ngp_ctx *ctx, int enable);
 int ngp_ctx_phase_cycles(ngp_ctx *ctx, int64_t *out_host, int reset);
 /* NeRFNetwork.forward (nerf/network_ff.py:51-74) in one kernel: xyzs,dirs [M,3] fp32 -> sigmas [M] fp32,

@@ -33,6 +33,7 @@ _SIGNATURES = {
     "ngp_ctx_destroy": [_p],
     "ngp_ctx_set_network": [_p, _p, _p, _p, _u32, _f32, _u32, _p, _u32, _p, _u32, _f32, _f32, _p],
     "ngp_ctx_set_scene": [_p, _p, _u32, _u32, _p, _f32],
+    "ngp_ctx_set_option": [_p, C.c_char_p, _u64],
     "ngp_ctx_enable_profile": [_p, _i32],
     "ngp_ctx_phase_cycles": [_p, _p, _i32],
     "ngp_network_forward": [_p, _p, _p, _u32, _i32, _p, _p, _p],
@@ -100,3 +101,24 @@ def require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:
             raise RuntimeError("nerfsafetyvalidation_b200: expected a CUDA tensor (there is no CPU fallback)")
+
+
+_FP_SAMPLES = 32
+
+
+def fingerprint(*tensors):
+    """Content fingerprint of parameter tensors: 32 evenly strided elements of each, read back in ONE device-to-host copy.
+    Part of the key of the fp16 weight caches: `param.data.copy_(...)` changes neither `_version` nor `data_ptr()`, and a
+    renderer that kept using the old cast would return wrong images without an error (the reference re-casts on every call)."""
+    import torch
+    parts = []
+    for t in tensors:
+        flat = t.detach().reshape(-1)
+        n = flat.numel()
+        if n == 0:
+            continue
+        step = max(1, n // _FP_SAMPLES)
+        parts.append(flat[::step][:_FP_SAMPLES].float())
+    if not parts:
+        return b""
+    return torch.cat(parts).cpu().numpy().tobytes()

@@ -42,7 +42,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         obj = os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
         if not force and _newer(obj, [src] + headers):
             return obj
-        cmd = [nvcc, *NVCC_FLAGS, "-Xptxas", "-v", "-c", src, "-o", obj]
+        # NGP_EXTRA_NVCC_FLAGS: development builds only (e.g. -DNGP_SPIN_TRAP: a barrier that never completes traps instead of hanging)
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("NGP_EXTRA_NVCC_FLAGS", "").split(), "-Xptxas", "-v", "-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = os.path.join(OBJ, os.path.basename(src)[:-3] + ".ptxas.log")
         with open(log, "w") as f:

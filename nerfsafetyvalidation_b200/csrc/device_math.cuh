@@ -104,6 +104,14 @@ __device__ __forceinline__ int mip_level(float mx, float cm1f) {
 __device__ __forceinline__ float march_dt(float t, const MarchConst &m) {
     return fminf(m.dt_max, fmaxf(m.dt_min, __fmul_rn(t, m.dt_gamma)));
 }
+// The (x, y, z, dt) the marcher attaches to a sample taken at ray parameter t (raymarching.cu:756-761): both are pure functions of
+// t and the ray, so the fused renderer's sample buffer stores t alone and every consumer recomputes them bit for bit.
+__device__ __forceinline__ float sample_dt(const MarchConst &m, float t) {
+    return m.dt_gamma == 0.0f ? fminf(m.dt_max, fmaxf(m.dt_min, 0.0f)) : march_dt(t, m);   // NaN-safe: fmaxf drops the NaN of inf * 0
+}
+__device__ __forceinline__ float sample_pos(const MarchConst &m, float o, float d, float t) {
+    return fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(d, t, o)));
+}
 
 // cell coordinate along one axis: clamp(0.5 * (x * mip_rbound + 1) * H, 0, H-1) truncated.
 // The reference evaluates the two products in double and narrows once; 0.5*a is exact and a*H is a

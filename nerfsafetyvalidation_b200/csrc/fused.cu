@@ -14,6 +14,9 @@
 #include <stddef.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <string.h>
+
+#include <initializer_list>
 
 #include "common.cuh"
 #include "device_math.cuh"
@@ -119,6 +122,27 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
         if (kLevelsPerTrip == 4) dst[trip * stride] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
         else if (kLevelsPerTrip == 2) reinterpret_cast<uint2 *>(dst + (trip >> 1) * stride)[trip & 1] = make_uint2(packed[0], packed[kLevelsPerTrip - 1]);
         else reinterpret_cast<uint32_t *>(dst + (trip >> 2) * stride)[trip & 3] = packed[0];
+    }
+}
+
+// 16-level hash-grid encoding of one point -> the 16 TMEM columns at taddr (this thread's lane).  tcgen05.st is warp-collective:
+// every lane calls this; lanes with !active store zeros without gathering (the reference's encoding of a point outside the unit
+// cube is zero as well, gridencoder.cu:99-123).
+template <int LPT>
+__device__ __forceinline__ void encode_point_tmem(const NetConst &nc, float x, float y, float z, bool active, uint32_t taddr) {
+    static_assert(LPT == 4 || LPT == 2, "a trip stores 4 or 2 columns");
+    float u0 = 0.f, u1 = 0.f, u2 = 0.f;
+    const bool inside = active && encode_unit(nc, x, y, z, u0, u1, u2);
+    // the trip loop is deliberately NOT unrolled: a small gather body keeps the warps of both roles inside the instruction cache
+#pragma unroll 1
+    for (int trip = 0; trip < 16 / LPT; trip++) {
+        uint32_t packed[LPT];
+#pragma unroll
+        for (int j = 0; j < LPT; j++) packed[j] = 0u;
+        if (inside) encode_trip<LPT>(nc, u0, u1, u2, trip, packed);
+        __syncwarp();
+        if (LPT == 4) tc::tmem_st4(taddr + (uint32_t)trip * 4u, make_uint4(packed[0], packed[1], packed[2], packed[LPT - 1]));
+        else tc::tmem_st2(taddr + (uint32_t)trip * 2u, packed[0], packed[1]);
     }
 }
 
@@ -285,20 +309,19 @@ __global__ void k_pack_network_tc(const __half *__restrict__ w_sigma, uint32_t n
     tc::pack_weight_chunks(w_color + 2048 + (size_t)nh_color * 4096, 16, 64, reinterpret_cast<uint4 *>(base + wm.cl), tid, nt, false);
 }
 
-// network_ff.py:51-74 with both MLPs on tcgen05: one warpgroup per CTA, thread = row of a 128-row tile.
+// network_ff.py:51-74 with both MLPs on tcgen05: one warpgroup per CTA, thread = row of a 128-row tile, activations in tensor memory.
 //   kDensityOnly: NeRFNetwork.density (network_ff.py:76-89) -- encoder + sigma net; `rgbs` is then a half [M,15] geo_feat buffer or NULL.
 template <bool kDensityOnly>
 __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const float *__restrict__ xyzs, const float *__restrict__ dirs, uint32_t M,
                                                             float *__restrict__ sigmas, void *__restrict__ rgbs_or_geo, uint32_t n_tiles) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
-    uint4 *s_a = s_w + nc.wtc_bytes / 16;
-    uint64_t *s_mbar = reinterpret_cast<uint64_t *>(s_a + 8 * tc::kRows);
+    uint64_t *s_mbar = reinterpret_cast<uint64_t *>(s_w + nc.wtc_bytes / 16);
     uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_mbar + 1);
     const int tid = threadIdx.x, warp = tid >> 5;
     for (uint32_t i = tid; i < nc.wtc_bytes / 16; i += blockDim.x) s_w[i] = __ldg(nc.wtc + i);
     tc::fence_async_smem();
-    if (warp == 0) tc::tmem_alloc(tc::smem_u32(s_tmem), tc::kTmemColsPerTile);
+    if (warp == 0) tc::tmem_alloc(tc::smem_u32(s_tmem), tc::kTmemColsTs);
     if (tid == 0) {
         tc::mbar_init(tc::smem_u32(s_mbar), 1);
         tc::mbar_init_fence();
@@ -308,19 +331,18 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
     tc::fence_after_sync();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(s_tmem);
     tc::Tile t;
-    t.a = s_a; t.a_saddr = tc::smem_u32(s_a); t.w_saddr = tc::smem_u32(s_w); t.mbar_saddr = tc::smem_u32(s_mbar);
+    t.w_saddr = tc::smem_u32(s_w); t.mbar_saddr = tc::smem_u32(s_mbar);
     t.tmem = tmem_base + ((uint32_t)(warp * 32) << 16); t.bar_id = 1; t.parity = 0;
-    t.e = s_a; t.e_saddr = t.a_saddr; t.aready_saddr = 0; t.parity_a = 0;
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint32_t row = tile * tc::kRows + tid;
         uint4 sh_lo = make_uint4(0, 0, 0, 0), sh_hi = sh_lo;
+        float x = 0.f, y = 0.f, z = 0.f;
         if (row < M) {
-            encode_point(nc, __ldg(xyzs + (size_t)row * 3), __ldg(xyzs + (size_t)row * 3 + 1), __ldg(xyzs + (size_t)row * 3 + 2), s_a + tid, tc::kRows);
+            x = __ldg(xyzs + (size_t)row * 3); y = __ldg(xyzs + (size_t)row * 3 + 1); z = __ldg(xyzs + (size_t)row * 3 + 2);
             if (!kDensityOnly)
                 sh_to_half(__ldg(dirs + (size_t)row * 3), __ldg(dirs + (size_t)row * 3 + 1), __ldg(dirs + (size_t)row * 3 + 2), sh_lo, sh_hi);
-        } else {
-            s_a[tid] = s_a[tc::kRows + tid] = s_a[2 * tc::kRows + tid] = s_a[3 * tc::kRows + tid] = make_uint4(0, 0, 0, 0);
         }
+        encode_point_tmem<4>(nc, x, y, z, row < M, t.tmem + tc::kColE);
         if (kDensityOnly) {
             float h[16];
             tc::sigma_tile128(t, tid, nc.nh_sigma, h);
@@ -344,11 +366,11 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc(tmem_base, tc::kTmemColsPerTile);
+    if (warp == 0) tc::tmem_dealloc(tmem_base, tc::kTmemColsTs);
 }
 
 // ---------------------------------------------------------------------------------------------- persistent renderer
-// NeRFRenderer.run_cuda's inference loop (nerf/renderer.py:329-376) as ONE persistent cooperative launch, one 16-warp CTA per
+// NeRFRenderer.run_cuda's inference loop (nerf/renderer.py:329-376) as ONE persistent cooperative launch, one 32-warp CTA per
 // SM.  The reference's global schedule `n_step = clamp(N // n_alive, 1, 8)` (renderer.py:357) decides where every ray's
 // chunks end, and a chunk boundary is visible in the result (rays_t restarts from the compositor's sum of deltas), so the
 // schedule is reproduced exactly -- but not by meeting once per iteration.  Two facts make that unnecessary:
@@ -366,44 +388,49 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
 //       correctness.
 //
 // Per epoch, two phases separated by a grid barrier (2 barriers per epoch instead of 2 per reference iteration):
-//   MARCH     lane-level dynamic scheduling: every LANE owns one live ray, probes the occupancy bitfield one cell per trip in
-//             lockstep with the other 31 lanes of its warp, and the moment its ray has its E*s samples (or left the box) the
-//             lane takes the next live ray from the list.  Samples go to a streaming buffer (20 B per sample, evict-first)
-//             laid out per 32-ray tile as [sample i][ray r] so the evaluator reads it fully coalesced.
-//   EVALUATE  a WARPGROUP pulls a 128-row tile: each of its 4 warps owns R = 32 / K consecutive live rays (adjacent pixels:
-//   + COMPOSITE  their samples share hash-grid cells) and evaluates K consecutive samples of each per pass: 16-level gather ->
-//             sigma MLP -> SH + colour MLP as tcgen05.mma on the 128 rows (weights resident in shared memory, accumulators in
-//             TMEM, tc_mlp.cuh), then the leader lane of every ray composites its K samples into the ray accumulators it
-//             holds in registers for the whole epoch (raymarching.cu:828-913), early termination included.
+//   MARCH     all 32 warps.  Lane-level dynamic scheduling: every LANE owns one live ray, probes the occupancy bitfield one cell
+//             per trip in lockstep with the other 31 lanes of its warp, and the moment its ray has its E*s samples (or left the
+//             box) the lane takes the next live ray from the list.  A sample is 8 bytes in the streaming buffer -- (t, delta_t);
+//             position and dt are pure functions of t -- laid out per 32-ray tile as [pass][ray][k] so the evaluator reads it
+//             fully coalesced.
+//   EVALUATE  WARP-SPECIALISED, four independent STREAMS per SM.  A stream walks 128-row tiles (4 warps x R = 32 / K
+//   + COMPOSITE  consecutive live rays x K consecutive samples per pass; thread = row = TMEM lane) through a producer /
+//             tensor-core / consumer pipeline that lives entirely in tensor memory (128 of the 512 TMEM columns per stream):
+//               gather team (4 warps)    16-level hash-grid gather of the pass's rows -> fp16 encoding written with tcgen05.st
+//                                        into one of two E slots (16 columns); the LAST warp to arrive issues layer 0
+//                                        (tcgen05.mma, A from TMEM, weights from shared memory) once the accumulators are free.
+//               epilogue team (4 warps)  per layer: tcgen05.ld of the accumulators D -> ReLU / fp16 -> tcgen05.st of the next
+//                                        operand H; the LAST warp to arrive issues the next layer.  After the sigma net: SH of
+//                                        the ray direction + geo features -> colour net; after the colour net: sigmoid and
+//                                        front-to-back compositing of the pass's K samples per ray in registers
+//                                        (raymarching.cu:828-913), early termination included.
+//             The gather of pass p + 1 and p + 2 runs under the seven-layer chain of pass p; nobody polls for anybody else's
+//             rows; no activation ever touches shared memory (which holds only the weights), so 200 KB of L1 serve the gather.
 //             Ray state makes one 32-byte round trip per EPOCH; dirs / sigmas / rgbs never exist in memory.
-#ifndef NGP_RENDER_THREADS
-#define NGP_RENDER_THREADS 640
+constexpr int kStreams = 4;                      // independent tile pipelines per SM
+constexpr int kGatherWarps = 4 * kStreams;       // warps 0 .. 15: stream = warp / 4, TMEM lane quadrant = warp % 4
+constexpr int kEpiWarps = 4 * kStreams;          // warps 16 .. 31: stream = (warp - 16) / 4
+constexpr int kRenderWarps = kGatherWarps + kEpiWarps;
+constexpr int kRenderThreads = kRenderWarps * 32;
+constexpr uint32_t kRenderTmemCols = 512;
+constexpr uint32_t kStreamCols = kRenderTmemCols / kStreams;   // D 0..63 | H 64..95 | E slot 0 96..111 | E slot 1 112..127
+static_assert(kStreamCols == 128 && tc::kColE + 32 == kStreamCols, "a stream owns 128 TMEM columns");
+// register budgets of the two roles during EVALUATE (setmaxnreg; the kernel launches with 64 per thread).  0 = leave it alone,
+// which is the default: moving 8 registers per thread from the epilogue to the gather warps measured 5 % SLOWER (12.36 vs 11.74 ms),
+// and the profiling build of the kernel hung with it.
+#ifndef NGP_GATHER_REGS
+#define NGP_GATHER_REGS 0
 #endif
-constexpr int kRenderThreads = NGP_RENDER_THREADS;   // whole warpgroups
-constexpr int kRenderWarps = kRenderThreads / 32;
-constexpr int kRenderGroups = kRenderWarps / 4;
-constexpr uint32_t kRenderTmemCols = kRenderGroups * 64 <= 256 ? 256 : 512;   // power of two >= 64 per warpgroup
-static_assert(kRenderThreads % 128 == 0 && kRenderGroups <= 8, "the renderer is built from warpgroups; TMEM holds 8 tiles");
-#ifndef NGP_TILE_CHUNKS
-#define NGP_TILE_CHUNKS 8
+#ifndef NGP_EPI_REGS
+#define NGP_EPI_REGS 0
 #endif
 #ifndef NGP_EXTRA_SMEM
 #define NGP_EXTRA_SMEM 0
 #endif
-// 16-byte chunks of a warpgroup's A tile: 8 of hidden activations (+ 4 of encoding staging; with 8 the staging aliases the first
-// four activation chunks, which are idle between the last layer of one pass and the first epilogue of the next)
-constexpr int kTileChunks = NGP_TILE_CHUNKS;
-// A/B switches (tools/ab_build.sh).  NGP_MIN_KSHIFT = 1 (K >= 2: 16 SH rows per warp) with NGP_COARSE_SMEM = 0 (coarse occupancy
-// read from global / L1) brings the CTA under the 132 KB carve-out (124 KB of L1 instead of 92); measured 12.8 ms vs 12.55 ms for
-// the defaults below -- the half-empty passes of the first epoch and the extra spills cost more than the L1 buys.
-#ifndef NGP_MIN_KSHIFT
-#define NGP_MIN_KSHIFT 0
-#endif
+// A/B switch (tools/ab_build.sh): NGP_COARSE_SMEM = 0 reads the coarse occupancy from global / L1 instead of shared memory.
 #ifndef NGP_COARSE_SMEM
 #define NGP_COARSE_SMEM 1
 #endif
-constexpr uint32_t kMinKShift = NGP_MIN_KSHIFT;
-constexpr int kShRows = 32 >> NGP_MIN_KSHIFT;   // SH rows (16 halves each) per warp
 constexpr int kMaxStep = 8;                    // renderer.py:357
 constexpr int kMaxEpoch = 128;                 // reference iterations per epoch (max_steps 1024 / n_step 8)
 #ifndef NGP_MAX_SAMPLES_PER_EPOCH
@@ -414,7 +441,7 @@ constexpr int kRefillLanes = 8;                // a warp refills its idle lanes 
 
 struct EpochCtr {
     uint32_t cursor;            // MARCH phase: next unclaimed entry of the live list
-    uint32_t ticket;            // EVALUATE phase: next unclaimed 32-ray tile
+    uint32_t ticket;            // EVALUATE phase: next unclaimed 128-row stream tile
     uint32_t n_out;             // survivors appended to the next live list
     uint32_t opaque;            // some ray of this epoch ended with weights_sum > 0.9: transmittance deaths are near
     uint32_t hist[kMaxEpoch];   // rays that died in iteration j of the epoch
@@ -424,6 +451,18 @@ struct RenderCtr {
     EpochCtr e[3];              // attempt a uses e[a % 3]; e[(a + 1) % 3] is zeroed during attempt a
     unsigned long long samples;
     uint32_t error;
+};
+
+// Tunables of the epoch policy (ngp_ctx_set_option); the defaults are what every committed number was measured with.
+struct RenderOptions {
+    uint32_t rows_per_ray = 32;   // sample-buffer rows per ray (one epoch's samples of every live ray must fit)
+    uint32_t max_epoch = 0;       // cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
+    uint32_t kshift = 4;          // >= 4: automatic; else log2 of the samples per ray per evaluation pass
+    uint32_t t_div = 2;           // once rays die by transmittance: E = margin / (t_div * rate)
+    uint32_t t_cap = 16;          // samples per epoch while transmittance deaths can still move n_step (0 = no cap)
+    uint32_t e0_cap = 4;          // cap on E of the first epoch (0 = none)
+    uint32_t rate0_div = 128;     // death-rate prior of the first epochs: N / rate0_div + 1 per iteration
+    uint32_t no_coarse = 0;       // 1 = do not build / use the coarse occupancy grid
 };
 
 struct RenderArgs {
@@ -439,8 +478,7 @@ struct RenderArgs {
     uint32_t *n_emit;  // [N] samples the marcher emitted for live-list entry n in this epoch
     const uint32_t *coarse;   // [coarse_words] 4x4x4-block occupancy bits (Morton order) or NULL
     uint32_t coarse_words;
-    float4 *smp_a;     // [cap_rows] (x, y, z, dt) per sample of the current epoch
-    float *smp_b;      // [cap_rows] t_new - last_t
+    float2 *smp;       // [cap_rows] (t, t_new - last_t) per sample of the current epoch
     uint32_t cap_rows;
     uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t force_kshift;   // >= 4: automatic; else log2 of the samples per ray per evaluation pass (profiling A/B)
@@ -450,7 +488,7 @@ struct RenderArgs {
     // replay throws away
     uint32_t cap_n[kMaxStep], cap_t[kMaxStep];
     uint32_t e0_cap;         // cap on E of the first epoch (0 = none): a short probe epoch learns cheaply whether rays die by transmittance
-    uint32_t rate0;          // death-rate prior for the first epochs: N / 128 + 1 deaths per iteration (NGP_RATE0_DIV overrides the 128)
+    uint32_t rate0;          // death-rate prior for the first epochs: N / 128 + 1 deaths per iteration
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -463,17 +501,17 @@ __device__ __forceinline__ uint32_t clamp_n_step(uint32_t N, uint32_t n_alive) {
     return q > (uint32_t)kMaxStep ? (uint32_t)kMaxStep : (q < 1u ? 1u : q);
 }
 
-// Tile geometry of one epoch: a tile is R = 32 / K consecutive live rays, one evaluation pass covers K consecutive samples of
-// each (lane = r * K + k).  K = 1 is "32 adjacent pixels, one sample each"; K = 8 gives 8x more (and 8x shorter) tiles, which is
-// what keeps 2368 warps evenly loaded once few rays are left.  Sample rows of a tile are stored [pass][ray][k], so a pass reads
-// 32 consecutive rows.
+// Tile geometry of one epoch: a warp tile is R = 32 / K consecutive live rays, one evaluation pass covers K consecutive samples
+// of each (lane = r * K + k).  K = 1 is "32 adjacent pixels, one sample each"; K = 8 gives 8x more (and 8x shorter) tiles, which
+// is what keeps the streams evenly loaded once few rays are left.  Sample rows of a tile are stored [pass][ray][k], so a pass
+// reads 32 consecutive rows.
 struct TileGeom {
     uint32_t kshift;   // log2 K
     uint32_t ESp;      // samples per ray rounded up to a multiple of K (row slots per ray)
 };
-__device__ __forceinline__ size_t sample_row0(const TileGeom &tg, uint32_t n) {
+__device__ __forceinline__ uint32_t sample_row0(const TileGeom &tg, uint32_t n) {   // < cap_rows < 2^31
     const uint32_t rshift = 5u - tg.kshift;
-    return (size_t)(n >> rshift) * ((32u >> tg.kshift) * tg.ESp) + ((n & ((1u << rshift) - 1u)) << tg.kshift);
+    return (n >> rshift) * ((32u >> tg.kshift) * tg.ESp) + ((n & ((1u << rshift) - 1u)) << tg.kshift);
 }
 
 // MARCH phase of one epoch for one warp (see the header comment): up to ES = E * s samples per live ray, in chunks of s.
@@ -483,7 +521,7 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
     bool has = false, list_done = false;
     uint32_t n = 0, emitted = 0, in_chunk = 0;
     const uint32_t kmask = (1u << tg.kshift) - 1u;
-    size_t row0 = 0;
+    uint32_t row0 = 0;
     float ox = 0.f, oy = 0.f, oz = 0.f, tm = 0.f, last_t = 0.f, far = 0.f, acc_t = 0.f;
     RayDir rd = make_ray_dir(1.f, 1.f, 1.f);
     for (;;) {
@@ -517,10 +555,10 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
         }
         if (has) {   // one lockstep probe
             float x, y, z, dt, dl;
+            const float t_at = tm;
             if (tm < far && march_probe(ra.mc, ox, oy, oz, rd, tm, last_t, x, y, z, dt, dl, s_coarse)) {
-                const size_t row = row0 + (size_t)(emitted >> tg.kshift) * 32 + (emitted & kmask);
-                __stcs(ra.smp_a + row, make_float4(x, y, z, dt));
-                __stcs(ra.smp_b + row, dl);
+                const uint32_t row = row0 + (emitted >> tg.kshift) * 32u + (emitted & kmask);
+                __stcs(ra.smp + row, make_float2(t_at, dl));
                 emitted++;
                 acc_t = __fadd_rn(acc_t, dl);           // what composite_rays will store to rays_t (raymarching.cu:870,905)
                 if (++in_chunk == s) {                  // chunk boundary: the next march call starts from rays_t (:723-725)
@@ -538,118 +576,293 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
     }
 }
 
-// EVALUATE + COMPOSITE phase of one epoch for one WARPGROUP (see the header comment).  The four warps of a group each own a
-// 32-row sub-tile (their own R rays) exactly as before, but walk their passes in lockstep so that the 128 rows go through the
-// MLPs as ONE tcgen05 tile (tc_mlp.cuh): thread = row = TMEM lane.
-struct GroupSmem {
-    uint32_t ticket[2];   // the group's current / next tile (claimed one tile ahead)
-    uint32_t max_ne[4];   // per-warp pass counts of the current tile
-    uint32_t pad[2];
+// ---- EVALUATE: the per-stream pipeline state in shared memory
+struct __align__(16) StreamSync {
+    uint64_t dfull;      // mbarrier, count 1: tcgen05.commit of every layer -- the accumulators D are complete
+    uint64_t empty[2];   // mbarrier, count 1: tcgen05.commit of layer 0 -- the E slot has been consumed (pre-armed once)
+    uint32_t cnt_e[2];   // per E slot: 4 gather-warp arrivals (the slot is filled) + 4 epilogue-warp arrivals (the previous pass has
+                         // let go of D); whoever brings it to 0 mod 8 issues layer 0 -- nobody waits for the other side
+    uint32_t cnt_h;      // epilogue-warp arrivals per layer (the warp that brings it to 0 mod 4 issues the next layer)
+    uint32_t ticket[2];  // the stream's current / next tile, claimed from EpochCtr::ticket by the team leader (gather warp 0) ...
+    uint32_t pad;
+    uint64_t tfull[2];   // ... mbarrier, count 1: the ticket is published
+    uint64_t tempty[2];  // ... mbarrier, count 7: the other seven warps of the stream have read it (pre-armed once)
+    unsigned long long dead[4];   // per lane quadrant: (tile + 1) << 32 | lanes whose ray has terminated -- a hint for the gather
 };
+__device__ __forceinline__ void stream_sync_init(StreamSync &ss) {   // one thread
+    tc::mbar_init(tc::smem_u32(&ss.dfull), 1);
+    tc::mbar_init(tc::smem_u32(&ss.empty[0]), 1);
+    tc::mbar_init(tc::smem_u32(&ss.empty[1]), 1);
+    ss.cnt_e[0] = 4u;   // D is free before the first pass: the four epilogue arrivals of slot 0 are pre-paid
+    ss.cnt_e[1] = ss.cnt_h = 0;
+    for (int i = 0; i < 2; i++) {
+        tc::mbar_init(tc::smem_u32(&ss.tfull[i]), 1);
+        tc::mbar_init(tc::smem_u32(&ss.tempty[i]), 7);
+    }
+    ss.dead[0] = ss.dead[1] = ss.dead[2] = ss.dead[3] = 0ull;
+}
+__device__ __forceinline__ void stream_sync_prearm(StreamSync &ss) {   // one thread, after the init fence: phase 0 of "free" is complete
+    for (int i = 0; i < 7; i++) {
+        tc::mbar_arrive(tc::smem_u32(&ss.tempty[0]));
+        tc::mbar_arrive(tc::smem_u32(&ss.tempty[1]));
+    }
+    tc::mbar_arrive(tc::smem_u32(&ss.empty[0]));
+    tc::mbar_arrive(tc::smem_u32(&ss.empty[1]));
+}
 
+// Rays and pass count of one 128-row stream tile, computed identically by the gather and the epilogue team (the two never
+// exchange anything but barrier arrivals): has_ray / n / ne of this lane's ray in warp tile 4 gtile + q, and the longest ray of
+// the four warp tiles.
+struct TileRays {
+    uint32_t n, ne, max_ne;
+    bool has_ray;
+};
+__device__ __forceinline__ TileRays tile_rays(const RenderArgs &ra, uint32_t gtile, int q, uint32_t my_r, uint32_t R, uint32_t n_alive, uint32_t ES) {
+    TileRays tr;
+    tr.ne = 0; tr.max_ne = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const uint32_t nj = (gtile * 4u + (uint32_t)j) * R + my_r;
+        const uint32_t e = nj < n_alive ? min(__ldcg(ra.n_emit + nj), ES) : 0u;   // ES may be shorter than what was marched (pre-validated epoch)
+        tr.max_ne = max(tr.max_ne, e);
+        if (j == q) tr.ne = e;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tr.max_ne = max(tr.max_ne, __shfl_xor_sync(0xffffffffu, tr.max_ne, o));
+    tr.n = (gtile * 4u + (uint32_t)q) * R + my_r;
+    tr.has_ray = tr.n < n_alive;
+    return tr;
+}
+
+// Dynamic tile scheduling inside a stream.  The eight warps of a stream walk the same sequence of tiles; tile number T of that
+// sequence (counted since the kernel started, like the pass counter) is claimed from the epoch's global ticket counter by the team
+// leader and handed to the other seven through a two-deep ring: all waits sleep in hardware, none polls.
+__device__ __forceinline__ uint32_t ticket_publish(StreamSync &ss, uint32_t *ticket_ctr, uint32_t T, int lane) {   // the leader warp
+    const uint32_t ts = T & 1u;
+    tc::mbar_wait(tc::smem_u32(&ss.tempty[ts]), (T >> 1) & 1u, 0x40000000u | T);
+    uint32_t t = 0;
+    if (lane == 0) {
+        t = atomicAdd(ticket_ctr, 1u);
+        *reinterpret_cast<volatile uint32_t *>(&ss.ticket[ts]) = t;
+        tc::mbar_arrive(tc::smem_u32(&ss.tfull[ts]));   // release: the ticket is visible to whoever sees the phase complete
+    }
+    return __shfl_sync(0xffffffffu, t, 0);
+}
+__device__ __forceinline__ uint32_t ticket_consume(StreamSync &ss, uint32_t T, int lane) {   // the other seven warps
+    const uint32_t ts = T & 1u;
+    tc::mbar_wait(tc::smem_u32(&ss.tfull[ts]), (T >> 1) & 1u, 0x50000000u | T);
+    const uint32_t t = *reinterpret_cast<volatile uint32_t *>(&ss.ticket[ts]);
+    __syncwarp();
+    if (lane == 0) tc::mbar_arrive(tc::smem_u32(&ss.tempty[ts]));
+    return t;
+}
+
+// Layer 0 of a pass (A = E slot, 32 -> 64), issued by whichever thread made the eighth arrival on the slot's counter.
+__device__ __forceinline__ void issue_layer0(uint32_t tmem_lane, uint32_t w_saddr, uint32_t slot, uint32_t empty_saddr, uint32_t dfull_saddr) {
+    tc::fence_after_sync();
+    const uint32_t base = tmem_lane & 0x0000FFFFu;
+#ifndef NGP_ABLATE_MLP
+    tc::issue_layer_ts(base + tc::kColD, base + tc::kColE + slot * 16u, w_saddr, 64, 32);
+#endif
+    tc::mma_commit(empty_saddr);   // the slot may be refilled ...
+    tc::mma_commit(dfull_saddr);   // ... and the epilogue team may read D once these MMAs have completed
+}
+
+// GATHER role of one warp: quadrant q (32 rows) of every pass of every tile of its stream.  P: passes this stream has issued since
+// the kernel started (selects the E slot and the barrier phases; identical in all eight warps of the stream).
 template <bool kProf>
-__device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs &ra, tc::Tile &tt, GroupSmem &gs, __half *s_sh, int lane, int wg_tid,
-                                           uint32_t lt_mask, const int *__restrict__ alive_in, int *__restrict__ alive_out,
-                                           const float4 *__restrict__ state_in, float4 *__restrict__ state_out, uint32_t n_alive,
-                                           uint32_t s, uint32_t ES, const TileGeom tg, uint32_t seq, EpochCtr *ec, uint32_t *s_hist,
-                                           long long (&pc)[8]) {
+__device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs &ra, StreamSync &ss, uint32_t tmem_lane, uint32_t w_saddr, int lane,
+                                            int q, uint32_t *ticket_ctr, const int *__restrict__ alive_in, uint32_t n_alive,
+                                            uint32_t ES, const TileGeom tg, uint32_t &P, uint32_t &T, long long (&pc)[8]) {
     const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
-    const uint32_t n_tiles = (n_alive + R - 1) / R;          // 32-row warp tiles
-    const uint32_t n_gtiles = (n_tiles + 3) / 4;             // 128-row group tiles
+    const uint32_t n_tiles = (n_alive + R - 1) / R, n_gtiles = (n_tiles + 3) / 4;
+    const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
+    const uint32_t tile_rows = R * tg.ESp;
+    const uint32_t empty_s = tc::smem_u32(&ss.empty[0]), cnt_s = tc::smem_u32(&ss.cnt_e[0]), dfull_s = tc::smem_u32(&ss.dfull);
+    const volatile unsigned long long *dead_w = &ss.dead[q];
+    long long c0 = kProf ? clock64() : 0, c1;
+#define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
+    const bool team_leader = q == 0;
+    uint32_t gtile = team_leader ? ticket_publish(ss, ticket_ctr, T, lane) : ticket_consume(ss, T, lane);
+    T++;
+    while (gtile < n_gtiles) {
+        uint32_t next_tile = 0;
+        if (team_leader) next_tile = ticket_publish(ss, ticket_ctr, T, lane);   // one tile ahead: the claim's latency hides behind this tile
+        const TileRays tr = tile_rays(ra, gtile, q, my_r, R, n_alive, ES);
+        float ox = 0.f, oy = 0.f, oz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
+        if (tr.has_ray) {
+            const int index = __ldcg(alive_in + tr.n);
+            const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
+            ox = __ldg(o); oy = __ldg(o + 1); oz = __ldg(o + 2);
+            dx = __ldg(d); dy = __ldg(d + 1); dz = __ldg(d + 2);
+        }
+        const uint32_t tbase = (gtile * 4u + (uint32_t)q) * tile_rows + (uint32_t)lane;
+        float t_next = 0.f;
+        if (my_k < tr.ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase));
+        NGP_PROF(0)
+        for (uint32_t i0 = 0; i0 < tr.max_ne; i0 += K, P++) {
+            const uint32_t slot = P & 1u;
+            tc::mbar_wait(empty_s + slot * 8u, (P >> 1) & 1u, 0x10000000u | P);   // layer 0 of pass P - 2 has consumed this slot
+            tc::fence_after_sync();
+            NGP_PROF(5)
+            const uint32_t i = i0 + my_k;
+            const unsigned long long dw = *dead_w;
+            const bool dead = (uint32_t)(dw >> 32) == gtile + 1u && (((uint32_t)dw >> lane) & 1u);
+            const bool active = tr.has_ray && i < tr.ne && !dead;
+            const float t = t_next;
+            if (!dead && i + K < tr.ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase + (i0 + K) * R));
+#ifdef NGP_ABLATE_GATHER   // ablation builds (tools/ab_build.sh): what does the frame cost without one of the two big phases?
+            const bool gather_on = false;   // the operand is all zeros: deterministic, so the epoch speculation still converges
+#else
+            const bool gather_on = true;
+#endif
+            encode_point_tmem<kRenderLevelsPerTrip>(nc, sample_pos(ra.mc, ox, dx, t), sample_pos(ra.mc, oy, dy, t), sample_pos(ra.mc, oz, dz, t),
+                                                    active && gather_on, tmem_lane + tc::kColE + slot * 16u);
+            tc::tmem_st_wait();
+            tc::fence_before_sync();
+            __syncwarp();
+            NGP_PROF(3)
+            if (lane == 0 && (tc::smem_arrive_count(cnt_s + slot * 4u) & 7u) == 7u)   // slot filled AND D free: issue layer 0
+                issue_layer0(tmem_lane, w_saddr, slot, empty_s + slot * 8u, dfull_s);
+            __syncwarp();
+            NGP_PROF(5)
+        }
+        if (!team_leader) next_tile = ticket_consume(ss, T, lane);
+        T++;
+        gtile = next_tile;
+        NGP_PROF(5)
+    }
+#undef NGP_PROF
+}
+
+// EPILOGUE role of one warp: quadrant q of its stream -- every layer's activation, then compositing, ray state and the next live list.
+// par: phase parity of ss.dfull (one phase per layer), persistent like P.
+template <bool kProf>
+__device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderArgs &ra, StreamSync &ss, uint32_t tmem_lane, uint32_t w_saddr,
+                                              float4 *scratch, int lane, int q, uint32_t lt_mask,
+                                              const int *__restrict__ alive_in, int *__restrict__ alive_out, const float4 *__restrict__ state_in,
+                                              float4 *__restrict__ state_out, uint32_t n_alive, uint32_t s, uint32_t ES, const TileGeom tg,
+                                              uint32_t seq, EpochCtr *ec, uint32_t *s_hist, uint32_t &P, uint32_t &T, uint32_t &par, long long (&pc)[8]) {
+    const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
+    const uint32_t n_tiles = (n_alive + R - 1) / R, n_gtiles = (n_tiles + 3) / 4;
     const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
     const bool leader = my_k == 0;
     const int lead_lane = lane & ~(int)(K - 1u);
-    const int wwarp = wg_tid >> 5;                           // warp within the group
-    const size_t tile_rows = (size_t)R * tg.ESp;
-    float4 *scratch = reinterpret_cast<float4 *>(tt.a + 4 * tc::kRows) + 2 * wg_tid;   // this row's 32 B in the idle half of the A tile
+    const uint32_t tile_rows = R * tg.ESp;
+    const uint32_t dfull_s = tc::smem_u32(&ss.dfull), cnt_s = tc::smem_u32(&ss.cnt_h), cnt_e_s = tc::smem_u32(&ss.cnt_e[0]),
+                   empty_s = tc::smem_u32(&ss.empty[0]);
+    const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
+    const int n_sig = 2 + (int)nc.nh_sigma, n_all = n_sig + 2 + (int)nc.nh_color;
+    const uint32_t t_d = tmem_lane + tc::kColD, t_h = tmem_lane + tc::kColH, base = tmem_lane & 0x0000FFFFu;
+    float4 *scr = scratch + 2 * lane;   // this lane's 32 bytes of its warp's compositing scratch
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
-    uint32_t par = 0;
-    if (wg_tid == 0) gs.ticket[0] = atomicAdd(&ec->ticket, 1u);
-    tc::group_sync(tt.bar_id);
-    uint32_t gtile = gs.ticket[0];
-    int nx_index = 0;
-    uint32_t nx_ne = 0;
-    if (gtile < n_gtiles) {
-        const uint32_t n = (gtile * 4 + wwarp) * R + my_r;
-        if (n < n_alive) { nx_index = __ldcg(alive_in + n); nx_ne = __ldcg(ra.n_emit + n); }
-    }
-    while (gtile < n_gtiles) {
-        const uint32_t tile = gtile * 4 + wwarp;
-        const bool has_ray = tile * R + my_r < n_alive;      // false for the whole warp if the group tile is ragged
-        const int index = nx_index;
-        const uint32_t ne = has_ray ? min(nx_ne, ES) : 0u;   // ES may be shorter than what was marched (pre-validated epoch)
-        uint32_t next_ticket = 0;
-        if (wg_tid == 0) next_ticket = atomicAdd(&ec->ticket, 1u);   // claimed now, published after the passes: its latency is hidden
-        const size_t tbase = (size_t)tile * tile_rows + lane;
-        float4 sa = make_float4(0.f, 0.f, 0.f, 0.f);
-        float sb = 0.f;
-        if (my_k < ne) { sa = __ldcs(ra.smp_a + tbase); sb = __ldcs(ra.smp_b + tbase); }
+    for (uint32_t gtile = ticket_consume(ss, T++, lane); gtile < n_gtiles; gtile = ticket_consume(ss, T++, lane)) {
+        NGP_PROF(6)
+        const TileRays tr = tile_rays(ra, gtile, q, my_r, R, n_alive, ES);
+        const uint32_t ne = tr.ne;
+        const bool has_ray = tr.has_ray;
+        int index = 0;
+        float dx = 0.f, dy = 0.f, dz = 1.f;
         RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         uint32_t samples = 0;
-        uint4 *srow = reinterpret_cast<uint4 *>(s_sh + my_r * 16);
-        if (has_ray && leader) {
-            const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
+        if (has_ray) {
+            index = __ldcg(alive_in + tr.n);
             const float *d = ra.rays_d + (size_t)index * 3;
-            sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), srow[0], srow[1]);   // the direction is constant along the ray
-            a.t = r0.x; a.ws = r0.y; a.d = r0.z; a.r = r1.x; a.g = r1.y; a.b = r1.z;
-            samples = __float_as_uint(r1.w);
+            dx = __ldg(d); dy = __ldg(d + 1); dz = __ldg(d + 2);   // the direction is constant along the ray: SH per pass from registers
+            if (leader) {
+                const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
+                a.t = r0.x; a.ws = r0.y; a.d = r0.z; a.r = r1.x; a.g = r1.y; a.b = r1.z;
+                samples = __float_as_uint(r1.w);
+            }
         }
-        uint32_t max_ne = ne;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) max_ne = max(max_ne, __shfl_xor_sync(0xffffffffu, max_ne, o));
-        if (lane == 0) gs.max_ne[wwarp] = max_ne;
-        tc::group_sync(tt.bar_id);                           // also orders the SH rows before their first read
-        max_ne = max(max(gs.max_ne[0], gs.max_ne[1]), max(gs.max_ne[2], gs.max_ne[3]));
-        bool dead = false;           // the ray of this lane (leader decides, group follows)
+        const uint32_t tbase = (gtile * 4u + (uint32_t)q) * tile_rows + (uint32_t)lane;
+        float2 sn = make_float2(0.f, 0.f);
+        if (my_k < ne) sn = __ldcg(ra.smp + tbase);
+        bool dead = false;           // the ray of this lane (leader decides, its K lanes follow)
         uint32_t death = 0;          // leader: iteration of the epoch this ray died in
         uint32_t chunk = 0, in_chunk = 0;   // leader: position of the next sample in the reference's chunking
-        uint4 *const erow = tt.e + wg_tid;
         NGP_PROF(0)
-        for (uint32_t i0 = 0; i0 < max_ne; i0 += K) {
+        for (uint32_t i0 = 0; i0 < tr.max_ne; i0 += K, P++) {
             const uint32_t i = i0 + my_k;
-            const bool active = !dead && i < ne;
-            uint32_t any;
-            asm volatile(
-                "{\n\t"
-                ".reg .pred p, q;\n\t"
-                "setp.ne.b32 q, %1, 0;\n\t"
-                "bar.red.or.pred p, %2, 128, q;\n\t"
-                "selp.u32 %0, 1, 0, p;\n\t"
-                "}\n"
-                : "=r"(any)
-                : "r"((uint32_t)active), "r"(tt.bar_id)
-                : "memory");
-            if (!any) break;
-            float sg, cr, cg, cbl;
-            const uint4 sh_lo = srow[0], sh_hi = srow[1];
-            const float4 ca = sa;
-            const float cb = sb;
-            if (!dead && i + K < ne) { sa = __ldcs(ra.smp_a + tbase + (size_t)(i0 + K) * R); sb = __ldcs(ra.smp_b + tbase + (size_t)(i0 + K) * R); }
-#ifndef NGP_ABLATE_GATHER   // ablation builds (tools/ab_build.sh): what does the frame cost without one of the two big phases?
-            if (active) encode_point<kRenderLevelsPerTrip>(nc, ca.x, ca.y, ca.z, erow, tc::kRows);
-#endif
-            NGP_PROF(3)
+            const bool active = has_ray && !dead && i < ne;
+            const float2 sc = sn;
+            if (!dead && i + K < ne) sn = __ldcg(ra.smp + tbase + (i0 + K) * R);
+            float sg = 0.f, cr = 0.f, cg = 0.f, cbl = 0.f;
 #ifndef NGP_ABLATE_MLP
-            tc::mlp_tile128_pipelined(tt, wg_tid, lane, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, cr, cg, cbl, [](int) {});
+#pragma unroll 1
+            for (int step = 0; step < n_all; step++) {
+                tc::mbar_wait(dfull_s, par, 0x30000000u | ((uint32_t)step << 24) | P);
+                par ^= 1u;
+                tc::fence_after_sync();
+                NGP_PROF(6)
+                const bool in_color = step >= n_sig;
+                const int l = in_color ? step - n_sig : step;                           // layer within its net
+                const bool last = l == (int)(in_color ? nc.nh_color : nc.nh_sigma) + 1;
+                if (last && in_color) {
+                    tc::rgb_from_acc(t_d, cr, cg, cbl);
+                    tc::fence_before_sync();
+                    __syncwarp();
+                    // D is free: that is one of the eight arrivals layer 0 of the NEXT pass needs; if its slot is already filled, issue it here
+                    const uint32_t nslot = (P + 1u) & 1u;
+                    if (lane == 0 && (tc::smem_arrive_count(cnt_e_s + nslot * 4u) & 7u) == 7u)
+                        issue_layer0(tmem_lane, w_saddr, nslot, empty_s + nslot * 8u, dfull_s);
+                    break;
+                }
+                uint32_t w_off, n_next, k_next;   // the layer that consumes what this step writes
+                if (!last) {
+                    tc::relu32_to_tmem(t_d, t_h);
+                    tc::relu32_to_tmem(t_d + 32, t_h + 16);
+                    const bool next_last = l + 1 == (int)(in_color ? nc.nh_color : nc.nh_sigma) + 1;
+                    w_off = (in_color ? wm.c0 : wm.s0) + 4096u + (uint32_t)l * 8192u;   // [32->64] is 4 KB, [64->64] 8 KB
+                    n_next = next_last ? 16u : 64u;
+                    k_next = 64u;
+                } else {   // end of the sigma net
+                    uint4 sh_lo, sh_hi;
+                    sh_to_half(dx, dy, dz, sh_lo, sh_hi);
+                    sg = tc::sigma_and_color_input(t_d, t_h, nc.density_scale, sh_lo, sh_hi);
+                    w_off = wm.c0; n_next = 64u; k_next = 32u;
+                }
+                tc::tmem_st_wait();
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0 && (tc::smem_arrive_count(cnt_s) & 3u) == 3u) {   // the operand is complete: issue the next layer
+                    tc::fence_after_sync();
+                    tc::issue_layer_ts(base + tc::kColD, base + tc::kColH, w_saddr + w_off, n_next, k_next);
+                    tc::mma_commit(dfull_s);
+                }
+                __syncwarp();
+                NGP_PROF(4)
+            }
 #else
-            sg = 1.0f + __uint_as_float(sh_lo.x & 1u); cr = cg = cbl = 0.5f;
+            {   // no MLPs: consume layer 0's (empty) commit, hand D back
+                tc::mbar_wait(dfull_s, par);
+                par ^= 1u;
+                tc::fence_after_sync();
+                sg = 1.0f + (float)(lane & 1); cr = cg = cbl = 0.5f;
+                tc::fence_before_sync();
+                __syncwarp();
+                const uint32_t nslot = (P + 1u) & 1u;
+                if (lane == 0 && (tc::smem_arrive_count(cnt_e_s + nslot * 4u) & 7u) == 7u)
+                    issue_layer0(tmem_lane, w_saddr, nslot, empty_s + nslot * 8u, dfull_s);
+            }
 #endif
+            const float dt = sample_dt(ra.mc, sc.x);
             if (K == 1) {
-                if (active && composite_sample(a, sg, cr, cg, cbl, ca.w, cb)) {   // raymarching.cu:866-894
+                if (active && composite_sample(a, sg, cr, cg, cbl, dt, sc.y)) {   // raymarching.cu:866-894
                     dead = true;
                     death = chunk;
                     samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
                 }
                 if (++in_chunk == s) { in_chunk = 0; chunk++; }
             } else {
-                scratch[0] = make_float4(sg, cr, cg, cbl);
-                scratch[1] = make_float4(ca.w, cb, 0.f, 0.f);
+                scr[0] = make_float4(sg, cr, cg, cbl);
+                scr[1] = make_float4(dt, sc.y, 0.f, 0.f);
                 __syncwarp();
                 if (leader && has_ray && !dead) {   // composite this pass's <= K samples of the ray in order
                     const uint32_t cnt = min(K, ne - min(ne, i0));
                     for (uint32_t k = 0; k < cnt; k++) {
-                        const float4 o = scratch[2 * k], dd = scratch[2 * k + 1];
+                        const float4 o = scr[2 * k], dd = scr[2 * k + 1];
                         if (composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y)) {
                             dead = true;
                             death = chunk;
@@ -660,6 +873,10 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
                     }
                 }
                 dead = __shfl_sync(0xffffffffu, dead, lead_lane);
+            }
+            {   // tell the gather team which rows it may skip from now on (a hint: a stale or foreign word only costs work)
+                const uint32_t dm = __ballot_sync(0xffffffffu, dead);
+                if (lane == 0) *reinterpret_cast<volatile unsigned long long *>(&ss.dead[q]) = ((unsigned long long)(gtile + 1u) << 32) | dm;
             }
             NGP_PROF(4)
         }
@@ -679,23 +896,23 @@ __device__ __forceinline__ void eval_phase(const NetConst &nc, const RenderArgs 
         }
         const uint32_t ballot = __ballot_sync(0xffffffffu, survives);   // renderer.py:369
         if (ballot) {
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(&ec->n_out, (uint32_t)__popc(ballot));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (survives) __stcg(alive_out + base + __popc(ballot & lt_mask), index);
+            uint32_t b0 = 0;
+            if (lane == 0) b0 = atomicAdd(&ec->n_out, (uint32_t)__popc(ballot));
+            b0 = __shfl_sync(0xffffffffu, b0, 0);
+            if (survives) __stcg(alive_out + b0 + __popc(ballot & lt_mask), index);
         }
-        // ---- next group tile
-        par ^= 1u;
-        if (wg_tid == 0) gs.ticket[par] = next_ticket;
-        tc::group_sync(tt.bar_id);   // publishes the ticket; also: everyone is done with this tile's SH rows and scratch
-        gtile = gs.ticket[par];
-        if (gtile < n_gtiles) {
-            const uint32_t n = (gtile * 4 + wwarp) * R + my_r;
-            if (n < n_alive) { nx_index = __ldcg(alive_in + n); nx_ne = __ldcg(ra.n_emit + n); }
-        }
-        NGP_PROF(5)
+        NGP_PROF(0)
     }
 #undef NGP_PROF
+}
+
+template <int kRegs>
+__device__ __forceinline__ void set_max_regs_inc() {
+    if (kRegs > 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs > 0 ? kRegs : 64));
+}
+template <int kRegs>
+__device__ __forceinline__ void set_max_regs_dec() {
+    if (kRegs > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs > 0 ? kRegs : 64));
 }
 
 template <bool kProf>
@@ -703,17 +920,17 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch], s_mval[kMaxEpoch];
-    __shared__ __align__(8) uint64_t s_mbar[kRenderGroups], s_aready[kRenderGroups];
-    __shared__ GroupSmem s_group[kRenderGroups];
+    __shared__ StreamSync s_sync[kStreams];
     __shared__ uint32_t s_tmem;
-    // dynamic shared memory: [tcgen05 weights][A tiles, 16 KB per warpgroup][SH rows, 32 B x kShRows per warp][coarse occupancy, optional]
+    // dynamic shared memory: [tcgen05 weights][compositing scratch, 1 KB per epilogue warp][coarse occupancy, optional]
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
-    uint4 *s_a = s_w + nc.wtc_bytes / 16;
-    __half *s_sh_all = reinterpret_cast<__half *>(s_a + (size_t)kRenderGroups * kTileChunks * tc::kRows);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, wg = warp >> 2, wg_tid = tid & 127;
+    float4 *s_scratch = reinterpret_cast<float4 *>(s_w + nc.wtc_bytes / 16);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool is_gather = warp < kGatherWarps;
+    const int stream = (warp & (kGatherWarps - 1)) >> 2, q = warp & 3;
     // coarse occupancy: a shared-memory copy (NGP_COARSE_SMEM) or the global array itself (4 KB, stays in L1)
     const bool coarse_in_smem = NGP_COARSE_SMEM != 0 && ra.coarse != nullptr;
-    uint32_t *s_coarse = coarse_in_smem ? reinterpret_cast<uint32_t *>(s_sh_all + (size_t)kRenderWarps * kShRows * 16) : const_cast<uint32_t *>(ra.coarse);
+    uint32_t *s_coarse = coarse_in_smem ? reinterpret_cast<uint32_t *>(s_scratch + (size_t)kEpiWarps * 64) : const_cast<uint32_t *>(ra.coarse);
     const uint32_t N = ra.N;
     const uint32_t lt_mask = (1u << lane) - 1u;
     long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -725,33 +942,18 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     if (tid < kMaxEpoch) s_hist[tid] = 0;
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(&s_tmem), kRenderTmemCols);
     if (tid == 0) {
-        for (int g = 0; g < kRenderGroups; g++) {
-            tc::mbar_init(tc::smem_u32(&s_mbar[g]), 1);
-#ifdef NGP_LAST_ARRIVER
-            s_aready[g] = 0;                                  // arrival counter (tc_mlp.cuh: layer_issue)
-#else
-            tc::mbar_init(tc::smem_u32(&s_aready[g]), 4);   // one arrival per warp of the group
-#endif
-        }
+        for (int g = 0; g < kStreams; g++) stream_sync_init(s_sync[g]);
         tc::mbar_init_fence();
+        for (int g = 0; g < kStreams; g++) stream_sync_prearm(s_sync[g]);
     }
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(&s_tmem);
-    tc::Tile tt;
-    tt.a = s_a + (size_t)wg * kTileChunks * tc::kRows;
-    tt.a_saddr = tc::smem_u32(tt.a);
-    tt.e = kTileChunks >= 12 ? tt.a + 8 * tc::kRows : tt.a;
-    tt.e_saddr = tc::smem_u32(tt.e);
-    tt.aready_saddr = tc::smem_u32(&s_aready[wg]);
-    tt.parity_a = 0;
-    tt.w_saddr = tc::smem_u32(s_w);
-    tt.mbar_saddr = tc::smem_u32(&s_mbar[wg]);
-    tt.tmem = tmem_base + (uint32_t)wg * tc::kTmemColsPerTile + ((uint32_t)((warp & 3) * 32) << 16);
-    tt.bar_id = 1u + (uint32_t)wg;
-    tt.parity = 0;
-    __half *s_sh = s_sh_all + (size_t)warp * kShRows * 16;
+    const uint32_t tmem_lane = tmem_base + (uint32_t)stream * kStreamCols + ((uint32_t)(q * 32) << 16);
+    const uint32_t w_saddr = tc::smem_u32(s_w);
+    StreamSync &ss = s_sync[stream];
+    uint32_t passes = 0, tiles = 0, par = 0;   // the stream's pipeline position (see gather_role / epilogue_role): lives across epochs
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
@@ -797,14 +999,13 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         for (;;) {   // tile geometry; shrink the epoch until its samples fit the buffer (rarely more than one trip)
             ES = E * s;
             tg.kshift = ra.force_kshift < 4u ? ra.force_kshift : (ES >= 5u ? 3u : (ES >= 3u ? 2u : ES - 1u));   // K = 8, 4, 2, 1
-            if (tg.kshift < kMinKShift) tg.kshift = kMinKShift;
             tg.ESp = (ES + (1u << tg.kshift) - 1u) & ~((1u << tg.kshift) - 1u);
             const uint32_t R = 32u >> tg.kshift;
             unsigned long long rows = (unsigned long long)((n_alive + R - 1) / R) * R * tg.ESp;
             if (rows <= ra.cap_rows) break;
             if (E > 1) { E = E > 8u ? E - 8u : E - 1u; continue; }
-            tg.kshift = kMinKShift;       // one iteration, minimal padding: (n_alive + 31) * (s + 1) <= 2 N + 279 rows always fits
-            tg.ESp = (ES + (1u << tg.kshift) - 1u) & ~((1u << tg.kshift) - 1u);
+            tg.kshift = 0;                // one iteration, minimal padding: (n_alive + 31) * (s + 1) <= 2 N + 279 rows always fits
+            tg.ESp = ES;
             break;
         }
         EpochCtr *ec = &ra.ctr->e[attempt % 3];
@@ -838,9 +1039,19 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             E = ok_iters;
             ES = E * s;
         }
+        if (tid < 4 * kStreams) s_sync[tid >> 2].dead[tid & 3] = 0ull;   // the skip hints are keyed by tile number: none survives an epoch
         __syncthreads();   // s_val is rewritten below
         if (kProf) pc[2] += clock64() - g0;
-        eval_phase<kProf>(nc, ra, tt, s_group[wg], s_sh, lane, wg_tid, lt_mask, alive_in, alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, pc);
+        if (is_gather) {
+            set_max_regs_inc<NGP_GATHER_REGS>();
+            gather_role<kProf>(nc, ra, ss, tmem_lane, w_saddr, lane, q, &ec->ticket, alive_in, n_alive, ES, tg, passes, tiles, pc);
+            set_max_regs_dec<NGP_GATHER_REGS ? 64 : 0>();
+        } else {
+            set_max_regs_dec<NGP_EPI_REGS>();
+            epilogue_role<kProf>(nc, ra, ss, tmem_lane, w_saddr, s_scratch + (size_t)(warp - kGatherWarps) * 64, lane, q, lt_mask, alive_in,
+                                 alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, passes, tiles, par, pc);
+            set_max_regs_inc<NGP_EPI_REGS ? 64 : 0>();
+        }
         if (kProf) g0 = clock64();
         __syncthreads();
         if (tid < kMaxEpoch) {
@@ -865,7 +1076,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             if (last != s_mval[j]) any_t = true;   // somebody died here without running out of samples: transmittance
         }
         __syncthreads();   // s_val is rewritten after the next epoch
-        if (kProf) pc[6] += clock64() - g0;
+        if (kProf) pc[7] += clock64() - g0;
         attempt++;
         if (!ok) {          // replay from the committed state with the E that is known to be valid
             E = ran;
@@ -887,6 +1098,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
 
     // ---- epilogue: background + depth normalisation (renderer.py:375-376) from the newest record of every ray
     uint32_t my_samples = 0;
+    const float poison = __ldcg(&ra.ctr->error) ? __uint_as_float(0x7fc00000u) : 0.0f;   // schedule check failed: no plausible-looking image
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
         float4 r0 = __ldcg(ra.state[0] + 2 * (size_t)n);
         const float4 q0 = __ldcg(ra.state[1] + 2 * (size_t)n);
@@ -894,7 +1106,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         if (second) r0 = q0;
         const float4 r1 = __ldcg(ra.state[second ? 1 : 0] + 2 * (size_t)n + 1);
         const float ws_n = r0.y;
-        const float k = __fmul_rn(__fsub_rn(1.0f, ws_n), ra.bg_color);
+        const float k = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, ws_n), ra.bg_color), poison);
         float *im = ra.image + (size_t)n * 3;
         im[0] = __fadd_rn(r1.x, k); im[1] = __fadd_rn(r1.y, k); im[2] = __fadd_rn(r1.z, k);
         ra.weights_sum[n] = ws_n;
@@ -906,8 +1118,11 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         my_samples += cnt;
     }
     if (kProf && lane == 0) {
-        pc[7] = clock64() - k_start;
-        pc[0] += pc[7] - (pc[0] + pc[1] + pc[2] + pc[3] + pc[4] + pc[5] + pc[6]);   // + prologue, epilogue, loop control
+        // slots: 0 tile set-up / tile end (both roles) + prologue, epilogue, loop control; 1 march; 2 barrier after march;
+        //        3 gather (sample load + 16 levels + store); 4 epilogue (activations, compositing); 5 gather team waiting (slot, D);
+        //        6 epilogue team waiting (layer commits); 7 barrier after evaluate
+        const long long total = clock64() - k_start;
+        pc[0] += total - (pc[0] + pc[1] + pc[2] + pc[3] + pc[4] + pc[5] + pc[6] + pc[7]);
         for (int k = 0; k < 8; k++) atomicAdd(reinterpret_cast<unsigned long long *>(ra.prof + k), (unsigned long long)pc[k]);
     }
     if (ra.stats) {
@@ -946,8 +1161,11 @@ struct ngp_ctx {
     // render workspace
     uint32_t capN = 0;
     uint32_t capRows = 0;
-    float *nears = nullptr, *fars = nullptr, *smp_b = nullptr;
-    float4 *smp_a = nullptr, *state[2] = {nullptr, nullptr};
+    float *nears = nullptr, *fars = nullptr;
+    float2 *smp = nullptr;
+    float4 *state[2] = {nullptr, nullptr};
+    RenderOptions opt;
+    uint32_t *h_error = nullptr;  // pinned host word: RenderCtr::error of the last *_host render
     uint32_t *n_emit = nullptr;
     int *alive[2] = {nullptr, nullptr};
     RenderCtr *ctr = nullptr;
@@ -964,7 +1182,13 @@ struct ngp_ctx {
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kRenderGroups * kTileChunks * tc::kRows * 16 + (size_t)kRenderWarps * kShRows * 32 + NGP_EXTRA_SMEM; }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kEpiWarps * 64 * sizeof(float4) + NGP_EXTRA_SMEM; }
+
+// Frees a set of device buffers and nulls the pointers (a failed re-allocation must not leave anything dangling).
+template <class... T>
+static void free_all(T *&...p) {
+    (void)std::initializer_list<int>{(cudaFree(p), p = nullptr, 0)...};
+}
 
 extern "C" {
 
@@ -989,7 +1213,8 @@ int ngp_ctx_create(ngp_ctx **out) {
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
     cudaFree(c->wpack); cudaFree(c->wtc); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
-    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
+    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp);
+    if (c->h_error) cudaFreeHost(c->h_error);
     cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws); cudaFree(c->d_poses);
     delete c;
     return 0;
@@ -1048,7 +1273,7 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
         if (int rc = after_launch("pack_network_tc")) return rc;
         nc.wtc = c->wtc;
         nc.wtc_bytes = wm.total;
-        c->fwd_tc_smem = wm.total + 8 * tc::kRows * 16 + 16;
+        c->fwd_tc_smem = wm.total + 16;
         NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
         NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
     }
@@ -1156,27 +1381,34 @@ int ngp_density_forward(ngp_ctx *c, const float *xyzs, uint32_t M, int apply_den
 }
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {
-    if (N <= c->capN) return 0;
-    cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
-    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp_a); cudaFree(c->smp_b);
-    c->capN = 0;
-    const uint32_t cap = N + N / 8 + 1024;
-    // sample buffer of one epoch: rows_per_ray * N rows of 20 B (streamed, evict-first); >= N + 256 rows always fits one iteration
-    static const char *rpr_env = getenv("NGP_ROWS_PER_RAY");
-    unsigned long long rpr = rpr_env ? strtoull(rpr_env, nullptr, 10) : 32ull;   // 64 saves an epoch on cfg2 A (-2 %) but lengthens the epochs that get replayed on terminating scenes (variant B 9.1 -> 12.7 ms)
-    if (rpr < 3) rpr = 3;
+    // sample buffer of one epoch: rows_per_ray * N rows of 8 B (streamed, evict-first); >= N + 256 rows always fits one iteration.
+    // 64 rows per ray save an epoch on cfg2 A (-2 %) but lengthen the epochs that get replayed on terminating scenes.
+    unsigned long long rpr = c->opt.rows_per_ray < 3u ? 3u : c->opt.rows_per_ray;
+    const uint32_t cap = N <= c->capN ? c->capN : N + N / 8 + 1024;
     unsigned long long rows = rpr * cap + 1024;
     if (rows > 0x7fffffffull) rows = 0x7fffffffull;
+    if (N <= c->capN && rows <= c->capRows) return 0;
     NGP_REQUIRE(rows >= 2ull * N + 512, "render: %u rays do not fit the sample buffer", N);
-    NGP_CUDA(cudaMalloc(&c->nears, sizeof(float) * cap));
-    NGP_CUDA(cudaMalloc(&c->fars, sizeof(float) * cap));
-    NGP_CUDA(cudaMalloc(&c->state[0], sizeof(float4) * 2 * (size_t)cap));
-    NGP_CUDA(cudaMalloc(&c->state[1], sizeof(float4) * 2 * (size_t)cap));
-    NGP_CUDA(cudaMalloc(&c->n_emit, sizeof(uint32_t) * cap));
-    NGP_CUDA(cudaMalloc(&c->alive[0], sizeof(int) * cap));
-    NGP_CUDA(cudaMalloc(&c->alive[1], sizeof(int) * cap));
-    NGP_CUDA(cudaMalloc(&c->smp_a, sizeof(float4) * (size_t)rows));
-    NGP_CUDA(cudaMalloc(&c->smp_b, sizeof(float) * (size_t)rows));
+    // all or nothing: the old buffers go first (they may be most of the memory), every pointer is nulled, and a failure part-way
+    // frees what it got and leaves an empty workspace behind
+    free_all(c->nears, c->fars, c->state[0], c->state[1], c->n_emit, c->alive[0], c->alive[1], c->smp);
+    c->capN = 0; c->capRows = 0;
+    cudaError_t e = cudaSuccess;
+    auto get = [&](auto *&ptr, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(&ptr, bytes); };
+    get(c->nears, sizeof(float) * cap);
+    get(c->fars, sizeof(float) * cap);
+    get(c->state[0], sizeof(float4) * 2 * (size_t)cap);
+    get(c->state[1], sizeof(float4) * 2 * (size_t)cap);
+    get(c->n_emit, sizeof(uint32_t) * cap);
+    get(c->alive[0], sizeof(int) * cap);
+    get(c->alive[1], sizeof(int) * cap);
+    get(c->smp, sizeof(float2) * (size_t)rows);
+    if (e != cudaSuccess) {
+        free_all(c->nears, c->fars, c->state[0], c->state[1], c->n_emit, c->alive[0], c->alive[1], c->smp);
+        cudaGetLastError();   // the failed cudaMalloc must not surface later as a bogus launch error
+        set_error("render: workspace for %u rays (%llu sample rows) could not be allocated: %s", N, rows, cudaGetErrorString(e));
+        return 2;
+    }
     c->capN = cap;
     c->capRows = (uint32_t)rows;
     return 0;
@@ -1190,42 +1422,35 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     NGP_DEVPTR(rays_o); NGP_DEVPTR(rays_d); NGP_DEVPTR(image); NGP_DEVPTR(depth); NGP_DEVPTR(weights_sum);
     if (int rc = ensure_workspace(c, N)) return rc;
     cudaStream_t st = as_stream(stream);
+#ifdef NGP_WATCHDOG
+    {
+        const int zero = 0;
+        NGP_CUDA(cudaMemcpyToSymbolAsync(tc::g_wd_abort, &zero, sizeof(int), 0, cudaMemcpyHostToDevice, st));
+    }
+#endif
     NGP_CUDA(cudaMemsetAsync(c->ctr, 0, sizeof(RenderCtr), st));
     RenderArgs ra{};
     ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps;
     for (int i = 0; i < 6; i++) ra.aabb[i] = c->aabb[i];
     ra.mc = make_march_const(c->nc.bound, dt_gamma, max_steps, c->cascade, c->grid_size, c->bitfield);
     ra.nears = c->nears; ra.fars = c->fars; ra.state[0] = c->state[0]; ra.state[1] = c->state[1]; ra.n_emit = c->n_emit;
-    ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1]; ra.smp_a = c->smp_a; ra.smp_b = c->smp_b; ra.cap_rows = c->capRows;
-    static const char *me_env = getenv("NGP_MAX_EPOCH");   // A/B switch for profiling only: 1 = one barrier pair per reference iteration
-    ra.max_epoch = me_env ? (uint32_t)strtoul(me_env, nullptr, 10) : 0u;
-    static const char *ks_env = getenv("NGP_KSHIFT");
-    ra.force_kshift = ks_env ? (uint32_t)strtoul(ks_env, nullptr, 10) : 4u;
-    static const char *td_env = getenv("NGP_T_DIV");
-    ra.t_div = td_env ? (uint32_t)strtoul(td_env, nullptr, 10) : 2u;
-    if (ra.t_div < 1u) ra.t_div = 1u;
-    static const char *tc_env = getenv("NGP_T_CAP");
-    {
-        const uint32_t t_cap = tc_env ? (uint32_t)strtoul(tc_env, nullptr, 10) : 16u;
-        for (uint32_t k = 1; k <= (uint32_t)kMaxStep; k++) {
-            const uint32_t n = (uint32_t)kMaxSamplesPerEpoch / k, t = (t_cap ? t_cap : (uint32_t)kMaxSamplesPerEpoch) / k;
-            ra.cap_n[k - 1] = n < 1u ? 1u : n;
-            ra.cap_t[k - 1] = t < 1u ? 1u : t;
-        }
+    ra.alive[0] = c->alive[0]; ra.alive[1] = c->alive[1]; ra.smp = c->smp; ra.cap_rows = c->capRows;
+    const RenderOptions &op = c->opt;
+    ra.max_epoch = op.max_epoch;
+    ra.force_kshift = op.kshift;
+    ra.t_div = op.t_div < 1u ? 1u : op.t_div;
+    for (uint32_t k = 1; k <= (uint32_t)kMaxStep; k++) {
+        const uint32_t n = (uint32_t)kMaxSamplesPerEpoch / k, t = (op.t_cap ? op.t_cap : (uint32_t)kMaxSamplesPerEpoch) / k;
+        ra.cap_n[k - 1] = n < 1u ? 1u : n;
+        ra.cap_t[k - 1] = t < 1u ? 1u : t;
     }
-    static const char *e0_env = getenv("NGP_E0_CAP");
-    ra.e0_cap = e0_env ? (uint32_t)strtoul(e0_env, nullptr, 10) : 4u;
-    static const char *r0_env = getenv("NGP_RATE0_DIV");
-    {
-        const uint32_t div = r0_env ? (uint32_t)strtoul(r0_env, nullptr, 10) : 128u;
-        ra.rate0 = N / (div ? div : 1u) + 1u;
-    }
+    ra.e0_cap = op.e0_cap;
+    ra.rate0 = N / (op.rate0_div ? op.rate0_div : 1u) + 1u;
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;
     size_t smem = c->render_smem;
-    static const bool no_coarse = getenv("NGP_NO_COARSE") != nullptr;   // A/B switch for profiling only
-    if (!no_coarse && c->coarse_words && smem + (NGP_COARSE_SMEM ? c->coarse_words * 4 : 0) <= c->render_smem_max) {
+    if (!op.no_coarse && c->coarse_words && smem + (NGP_COARSE_SMEM ? c->coarse_words * 4 : 0) <= c->render_smem_max) {
         const uint32_t n_blocks = c->coarse_words * 32;
         k_coarse_occupancy<<<div_up(n_blocks, 256), 256, 0, st>>>(reinterpret_cast<const unsigned long long *>(c->bitfield), n_blocks, c->coarse);
         if (int rc = after_launch("coarse_occupancy")) return rc;
@@ -1239,17 +1464,39 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     return after_launch("render");
 }
 
-static int ensure_host_staging(ngp_ctx *c, uint32_t N) {
-    if (N > c->capHost) {
-        cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws);
+static int ensure_host_staging(ngp_ctx *c, uint32_t N, uint32_t F) {
+    if (!c->h_error) NGP_CUDA(cudaMallocHost(&c->h_error, sizeof(uint32_t)));
+    if (N > c->capHost) {   // all or nothing, as ensure_workspace
+        free_all(c->d_o, c->d_d, c->d_img, c->d_depth, c->d_ws);
         c->capHost = 0;
-        NGP_CUDA(cudaMalloc(&c->d_o, sizeof(float) * 3 * (size_t)N));
-        NGP_CUDA(cudaMalloc(&c->d_d, sizeof(float) * 3 * (size_t)N));
-        NGP_CUDA(cudaMalloc(&c->d_img, sizeof(float) * 3 * (size_t)N));
-        NGP_CUDA(cudaMalloc(&c->d_depth, sizeof(float) * (size_t)N));
-        NGP_CUDA(cudaMalloc(&c->d_ws, sizeof(float) * (size_t)N));
+        cudaError_t e = cudaSuccess;
+        auto get = [&](float *&ptr, size_t n) { if (e == cudaSuccess) e = cudaMalloc(&ptr, sizeof(float) * n); };
+        get(c->d_o, 3 * (size_t)N); get(c->d_d, 3 * (size_t)N); get(c->d_img, 3 * (size_t)N); get(c->d_depth, N); get(c->d_ws, N);
+        if (e != cudaSuccess) {
+            free_all(c->d_o, c->d_d, c->d_img, c->d_depth, c->d_ws);
+            cudaGetLastError();
+            set_error("render_host: staging for %u rays could not be allocated: %s", N, cudaGetErrorString(e));
+            return 2;
+        }
         c->capHost = N;
     }
+    if (F > c->capPoses) {
+        free_all(c->d_poses);
+        c->capPoses = 0;
+        NGP_CUDA(cudaMalloc(&c->d_poses, sizeof(float) * 16 * (size_t)F));
+        c->capPoses = F;
+    }
+    return 0;
+}
+
+// image + depth back to the host, then the kernel's own consistency word: a render whose death histogram and live list disagreed
+// (RenderCtr::error) is reported, not returned as an image
+static int finish_host_render(ngp_ctx *c, uint32_t N, float *image_host, float *depth_host, cudaStream_t st, const char *what) {
+    NGP_CUDA(cudaMemcpyAsync(image_host, c->d_img, sizeof(float) * 3 * (size_t)N, cudaMemcpyDeviceToHost, st));
+    NGP_CUDA(cudaMemcpyAsync(depth_host, c->d_depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st));
+    NGP_CUDA(cudaMemcpyAsync(c->h_error, &c->ctr->error, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    NGP_CUDA(cudaStreamSynchronize(st));
+    NGP_REQUIRE(*c->h_error == 0u, "%s: the renderer's schedule check failed (death histogram and live list disagree); the image is poisoned with NaN", what);
     return 0;
 }
 
@@ -1258,15 +1505,12 @@ int ngp_render_host(ngp_ctx *c, const float *rays_o_host, const float *rays_d_ho
     NGP_REQUIRE(c != nullptr, "render_host: null ctx");
     NGP_REQUIRE(rays_o_host && rays_d_host && image_host && depth_host, "render_host: null host pointer");
     if (N == 0) return 0;
-    if (int rc = ensure_host_staging(c, N)) return rc;
+    if (int rc = ensure_host_staging(c, N, 0)) return rc;
     cudaStream_t st = as_stream(stream);
     NGP_CUDA(cudaMemcpyAsync(c->d_o, rays_o_host, sizeof(float) * 3 * (size_t)N, cudaMemcpyHostToDevice, st));
     NGP_CUDA(cudaMemcpyAsync(c->d_d, rays_d_host, sizeof(float) * 3 * (size_t)N, cudaMemcpyHostToDevice, st));
     if (int rc = ngp_render(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, c->d_img, c->d_depth, c->d_ws, nullptr, nullptr, stream)) return rc;
-    NGP_CUDA(cudaMemcpyAsync(image_host, c->d_img, sizeof(float) * 3 * (size_t)N, cudaMemcpyDeviceToHost, st));
-    NGP_CUDA(cudaMemcpyAsync(depth_host, c->d_depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st));
-    NGP_CUDA(cudaStreamSynchronize(st));
-    return 0;
+    return finish_host_render(c, N, image_host, depth_host, st, "render_host");
 }
 
 int ngp_render_poses_host(ngp_ctx *c, const float *poses_host, uint32_t F, uint32_t H, uint32_t W, float fx, float fy, float cx, float cy,
@@ -1277,21 +1521,30 @@ int ngp_render_poses_host(ngp_ctx *c, const float *poses_host, uint32_t F, uint3
     if (n == 0) return 0;
     NGP_REQUIRE(n <= 0xffffffffull, "render_poses_host: %llu rays exceed the 32-bit ray index of the renderer", n);
     const uint32_t N = (uint32_t)n;
-    if (int rc = ensure_host_staging(c, N)) return rc;
-    if (F > c->capPoses) {
-        cudaFree(c->d_poses);
-        c->capPoses = 0;
-        NGP_CUDA(cudaMalloc(&c->d_poses, sizeof(float) * 16 * (size_t)F));
-        c->capPoses = F;
-    }
+    if (int rc = ensure_host_staging(c, N, F)) return rc;
     cudaStream_t st = as_stream(stream);
     NGP_CUDA(cudaMemcpyAsync(c->d_poses, poses_host, sizeof(float) * 16 * (size_t)F, cudaMemcpyHostToDevice, st));   // 64 B per frame
     if (int rc = ngp_get_rays(c->d_poses, F, H, W, fx, fy, cx, cy, c->d_o, c->d_d, stream)) return rc;
     if (int rc = ngp_render(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, c->d_img, c->d_depth, c->d_ws, nullptr, nullptr, stream)) return rc;
-    NGP_CUDA(cudaMemcpyAsync(image_host, c->d_img, sizeof(float) * 3 * (size_t)N, cudaMemcpyDeviceToHost, st));
-    NGP_CUDA(cudaMemcpyAsync(depth_host, c->d_depth, sizeof(float) * (size_t)N, cudaMemcpyDeviceToHost, st));
-    NGP_CUDA(cudaStreamSynchronize(st));
-    return 0;
+    return finish_host_render(c, N, image_host, depth_host, st, "render_poses_host");
+}
+
+// Tunables of the renderer's epoch policy, per context (no process-wide state).  Unknown names are an error.
+int ngp_ctx_set_option(ngp_ctx *c, const char *name, uint64_t value) {
+    NGP_REQUIRE(c != nullptr && name != nullptr, "ctx_set_option: null argument");
+    const struct { const char *name; uint32_t RenderOptions::*field; } table[] = {
+        {"rows_per_ray", &RenderOptions::rows_per_ray}, {"max_epoch", &RenderOptions::max_epoch}, {"kshift", &RenderOptions::kshift},
+        {"t_div", &RenderOptions::t_div}, {"t_cap", &RenderOptions::t_cap}, {"e0_cap", &RenderOptions::e0_cap},
+        {"rate0_div", &RenderOptions::rate0_div}, {"no_coarse", &RenderOptions::no_coarse},
+    };
+    for (const auto &t : table)
+        if (strcmp(t.name, name) == 0) {
+            NGP_REQUIRE(value <= 0xffffffffull, "ctx_set_option: %s = %llu does not fit 32 bits", name, (unsigned long long)value);
+            c->opt.*(t.field) = (uint32_t)value;
+            return 0;
+        }
+    NGP_REQUIRE(false, "ctx_set_option: unknown option '%s' (rows_per_ray, max_epoch, kshift, t_div, t_cap, e0_cap, rate0_div, no_coarse)", name);
+    return 1;
 }
 
 }  // extern "C"

@@ -16,6 +16,7 @@
 #pragma once
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "device_math.cuh"
 
@@ -59,24 +60,40 @@ __device__ __forceinline__ void mbar_arrive(uint32_t mbar_saddr) {   // release 
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mbar_saddr) : "memory");
 }
 __device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void mbar_wait(uint32_t mbar_saddr, uint32_t parity) {
+// Development builds (-DNGP_WATCHDOG): a wait that lasts longer than ~2 s raises a device-wide abort flag, reports who waited for
+// what (`info` is the caller's tag) and returns; every other wait then returns too, so the kernel ends and the report is flushed.
+#ifdef NGP_WATCHDOG
+__device__ int g_wd_abort;
+#endif
+__device__ __forceinline__ void mbar_wait(uint32_t mbar_saddr, uint32_t parity, uint32_t info = 0) {
     uint32_t done = 0;
-#ifdef NGP_SPIN_TRAP
+#ifdef NGP_WATCHDOG
     uint32_t spins = 0;
+    const long long t0 = clock64();
 #endif
     do {
-#ifdef NGP_SPIN_TRAP   // development builds: a tensor-core commit that never arrives traps instead of hanging the device
-        if (++spins == (1u << 28)) __trap();
-#endif
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"   // %3: suspend-time hint -- sleep in hardware, do not poll
             "selp.u32 %0, 1, 0, p;\n\t"
             "}\n"
             : "=r"(done)
-            : "r"(mbar_saddr), "r"(parity)
+            : "r"(mbar_saddr), "r"(parity), "r"(0x989680u)
             : "memory");
+#ifdef NGP_WATCHDOG
+        if (!done && (++spins & 255u) == 0u) {
+            if (*reinterpret_cast<volatile int *>(&g_wd_abort)) break;
+            if (clock64() - t0 > 4000000000ll) {
+                atomicExch(&g_wd_abort, 1);
+                printf("WATCHDOG block %d warp %d lane %d: barrier 0x%x parity %u info 0x%x\n", (int)blockIdx.x, (int)(threadIdx.x >> 5),
+                       (int)(threadIdx.x & 31), mbar_saddr, parity, info);
+                break;
+            }
+        }
+#else
+        (void)info;
+#endif
     } while (!done);
 }
 
@@ -114,6 +131,75 @@ __device__ __forceinline__ void tmem_ld4(uint32_t taddr, float (&v)[4]) {
     for (int i = 0; i < 4; i++) v[i] = __uint_as_float(r[i]);
 }
 
+// ---- A operand in tensor memory (the renderer's pipeline): row r of A lives in TMEM lane r, halves (2c, 2c + 1) of the row in
+//      32-bit column c -- the layout a row-per-thread tcgen05.st.32x32b writes (cute: tmem_frg_1sm<half, half>, M = 128).
+//      One K = 16 MMA consumes 8 columns.
+__device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st2(uint32_t taddr, uint32_t a, uint32_t b) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, const uint4 &v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+                 "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+}
+// 16 accumulator columns -> ReLU -> 8 packed fp16 columns of the next A operand (same lane)
+__device__ __forceinline__ void relu16_to_tmem(uint32_t t_src, uint32_t t_dst) {
+    float v[16];
+    tmem_ld16(t_src, v);
+    uint32_t p[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) p[i] = pack_half2_relu(v[2 * i], v[2 * i + 1]);
+    tmem_st8(t_dst, p);
+}
+// 32 accumulator columns -> ReLU -> 16 packed fp16 columns: half as many TMEM round trips per layer as the 16-column form
+__device__ __forceinline__ void relu32_to_tmem(uint32_t t_src, uint32_t t_dst) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, "
+        "%22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+          "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+          "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]),
+          "=r"(r[31])
+        : "r"(t_src)
+        : "memory");
+    tmem_ld_wait();
+    uint32_t p[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) p[i] = pack_half2_relu(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(t_dst),
+                 "r"(p[0]), "r"(p[1]), "r"(p[2]), "r"(p[3]), "r"(p[4]), "r"(p[5]), "r"(p[6]), "r"(p[7]), "r"(p[8]), "r"(p[9]), "r"(p[10]), "r"(p[11]),
+                 "r"(p[12]), "r"(p[13]), "r"(p[14]), "r"(p[15])
+                 : "memory");
+}
+// The K / 16 MMAs of one layer with A in tensor memory, issued by ONE thread.  tmem_d / tmem_a: lane 0, first column.
+__device__ __forceinline__ void issue_layer_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t w_saddr, uint32_t N, uint32_t K) {
+    const uint32_t idesc = instr_desc(N);
+    for (uint32_t k = 0; k < K / 16; k++) {
+        const uint64_t bd = smem_desc(w_saddr + k * 2 * (N * 16), N * 16, 128);
+        mma_f16_ts(tmem_d, tmem_a + k * 8, bd, idesc, k > 0 ? 1u : 0u);
+    }
+}
+// CTA-scope acq_rel arrival counter in shared memory: returns the value before the increment
+__device__ __forceinline__ uint32_t smem_arrive_count(uint32_t saddr) {
+    uint32_t old;
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(saddr) : "memory");
+    return old;
+}
+
 // ---- packed weights: per layer uint4 [K / 8][N], layers in evaluation order
 struct WeightMap {   // byte offsets into the packed blob
     uint32_t s0, sh, sl, c0, ch, cl, total;
@@ -147,37 +233,30 @@ __device__ __forceinline__ void pack_weight_chunks(const __half *__restrict__ W,
     }
 }
 
-// ---- per-warpgroup tile resources
+// ---- one warpgroup, one 128-row tile, activations in tensor memory (the stand-alone network kernels)
+// TMEM columns of a tile, relative to its base: accumulators D, hidden activations H (64 halves = 32 columns), and the first
+// layer's operand E (the 32-half hash-grid encoding = 16 columns).
+constexpr uint32_t kColD = 0, kColH = 64, kColE = 96;
+constexpr uint32_t kTmemColsTs = 128;   // power of two >= 112
+
 struct Tile {
-    uint4 *a;             // A operand: uint4 [8][128] (16 KB), generic pointer
-    uint32_t a_saddr;     // its shared-space address
     uint32_t w_saddr;     // packed weights (shared-space address of the blob)
     uint32_t mbar_saddr;  // one mbarrier (count 1) owned by this warpgroup
-    uint32_t tmem;        // TMEM address of this tile's 64 accumulator columns, lane field = this WARP's first lane
+    uint32_t tmem;        // TMEM address of the tile's first column, lane field = this WARP's first lane
     uint32_t bar_id;      // named barrier of this warpgroup (1..15)
     uint32_t parity;      // phase of the mbarrier
-    // pipelined variant only (mlp_tile128_pipelined)
-    uint4 *e;             // encoding staging: uint4 [4][128] (8 KB), the first layer's A operand
-    uint32_t e_saddr;
-    uint32_t aready_saddr;   // mbarrier (count 4): every warp of the group has stored its rows of the next A operand
-    uint32_t parity_a;
 };
 
-// One layer: D[128 x N] (TMEM) = A[128 x K] (smem) * W[N x K]^T (smem).  All 128 threads of the warpgroup call it after having
-// written their A rows with ordinary stores; on return the accumulators are readable with tcgen05.ld.
-__device__ __forceinline__ void layer_mma(Tile &t, int row, uint32_t w_off, uint32_t N, uint32_t K) {
-    fence_async_smem();      // this thread's A-row stores -> visible to the tensor core's (async proxy) reads
-    fence_before_sync();     // this thread's tcgen05.ld of the previous accumulators are ordered before the barrier
+// One layer: D[128 x N] = A[128 x K] (TMEM columns a_col ..) * W[N x K]^T (smem).  All 128 threads call it after their tcgen05.st of
+// the A rows; on return the accumulators are readable with tcgen05.ld.
+__device__ __forceinline__ void layer_ts(Tile &t, int row, uint32_t a_col, uint32_t w_off, uint32_t N, uint32_t K) {
+    tmem_st_wait();          // this thread's A-row stores have landed in tensor memory
+    fence_before_sync();     // ... and are ordered, with its tcgen05.ld of the previous accumulators, before the barrier
     group_sync(t.bar_id);
     if (row == 0) {
         fence_after_sync();
-        const uint32_t idesc = instr_desc(N);
-        const uint32_t tmem_d = t.tmem & 0x0000FFFFu;   // lane 0 of the tile's columns
-        for (uint32_t k = 0; k < K / 16; k++) {
-            const uint64_t ad = smem_desc(t.a_saddr + k * 2 * (kRows * 16), kRows * 16, 128);
-            const uint64_t bd = smem_desc(t.w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
-            mma_f16_ss(tmem_d, ad, bd, idesc, k > 0 ? 1u : 0u);
-        }
+        const uint32_t base = t.tmem & 0x0000FFFFu;   // lane 0
+        issue_layer_ts(base + kColD, base + a_col, t.w_saddr + w_off, N, K);
         mma_commit(t.mbar_saddr);
         mbar_wait(t.mbar_saddr, t.parity);   // one poller per warpgroup; the other 127 threads sleep in the hardware barrier below
     }
@@ -185,59 +264,54 @@ __device__ __forceinline__ void layer_mma(Tile &t, int row, uint32_t w_off, uint
     group_sync(t.bar_id);
     fence_after_sync();
 }
-
-// ReLU + fp16 rounding of this thread's 64 accumulators -> its row of the next A operand (8 chunks).
-__device__ __forceinline__ void relu_row_to_a(const Tile &t, int row) {
+__device__ __forceinline__ void relu_row_ts(const Tile &t) {
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-        float v[16];
-        tmem_ld16(t.tmem + q * 16, v);
-        t.a[(2 * q) * kRows + row] = make_uint4(pack_half2_relu(v[0], v[1]), pack_half2_relu(v[2], v[3]), pack_half2_relu(v[4], v[5]), pack_half2_relu(v[6], v[7]));
-        t.a[(2 * q + 1) * kRows + row] =
-            make_uint4(pack_half2_relu(v[8], v[9]), pack_half2_relu(v[10], v[11]), pack_half2_relu(v[12], v[13]), pack_half2_relu(v[14], v[15]));
-    }
+    for (int q = 0; q < 4; q++) relu16_to_tmem(t.tmem + kColD + q * 16, t.tmem + kColH + q * 8);
+}
+// sigma-net output row (16 accumulators) -> sigma, and the colour net's first operand [SH16 | 0, geo15] in H columns 0..15
+__device__ __forceinline__ float sigma_and_color_input(uint32_t t_d, uint32_t t_h, float density_scale, const uint4 &sh_lo, const uint4 &sh_hi) {
+    float v[16];
+    tmem_ld16(t_d, v);
+    uint32_t g0 = pack_half2(v[0], v[1]);
+    const float sigma = expf(__half2float(__ushort_as_half((unsigned short)(g0 & 0xffffu)))) * density_scale;
+    g0 &= 0xffff0000u;   // column 0 (log-density) is not a colour feature
+    tmem_st4(t_h, sh_lo);
+    tmem_st4(t_h + 4, sh_hi);
+    tmem_st4(t_h + 8, make_uint4(g0, pack_half2(v[2], v[3]), pack_half2(v[4], v[5]), pack_half2(v[6], v[7])));
+    tmem_st4(t_h + 12, make_uint4(pack_half2(v[8], v[9]), pack_half2(v[10], v[11]), pack_half2(v[12], v[13]), pack_half2(v[14], v[15])));
+    return sigma;
+}
+__device__ __forceinline__ void rgb_from_acc(uint32_t t_d, float &r, float &g, float &b) {
+    float v[4];
+    tmem_ld4(t_d, v);
+    const float h0 = __half2float(__float2half_rn(v[0])), h1 = __half2float(__float2half_rn(v[1])), h2 = __half2float(__float2half_rn(v[2]));
+    r = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h0))));
+    g = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h1))));
+    b = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h2))));
 }
 
-// Both MLPs for the 128 rows of one warpgroup.  Precondition: every thread stored the 4 chunks of its row's hash-grid encoding
-// (32 halves) to t.a[c * 128 + row], c = 0..3.  sh_lo / sh_hi: the row's 16 SH halves.  Returns this row's sigma and rgb with the
-// dtype flow of the reference under autocast (network_ff.py:56-72): sigma = exp(float(half h0)) * density_scale,
-// rgb = half(sigmoid(float(half h))).
+// Both MLPs for the 128 rows of one warpgroup.  Precondition: every thread stored its row's hash-grid encoding (32 halves) to the
+// 16 TMEM columns at kColE.  sh_lo / sh_hi: the row's 16 SH halves.  Returns this row's sigma and rgb with the dtype flow of the
+// reference under autocast (network_ff.py:56-72): sigma = exp(float(half h0)) * density_scale, rgb = half(sigmoid(float(half h))).
 __device__ __forceinline__ void mlp_tile128(Tile &t, int row, uint32_t nh_sigma, uint32_t nh_color, float density_scale, const uint4 &sh_lo,
                                             const uint4 &sh_hi, float &sigma, float &r, float &g, float &b) {
     const WeightMap wm = weight_map(nh_sigma, nh_color);
-    layer_mma(t, row, wm.s0, 64, 32);
-    relu_row_to_a(t, row);
+    layer_ts(t, row, kColE, wm.s0, 64, 32);
+    relu_row_ts(t);
     for (uint32_t k = 0; k < nh_sigma; k++) {
-        layer_mma(t, row, wm.sh + k * 8 * 64 * 16, 64, 64);
-        relu_row_to_a(t, row);
+        layer_ts(t, row, kColH, wm.sh + k * 8 * 64 * 16, 64, 64);
+        relu_row_ts(t);
     }
-    layer_mma(t, row, wm.sl, 16, 64);
-    {
-        float v[16];
-        tmem_ld16(t.tmem, v);
-        uint32_t g0 = pack_half2(v[0], v[1]);
-        sigma = expf(__half2float(__ushort_as_half((unsigned short)(g0 & 0xffffu)))) * density_scale;
-        g0 &= 0xffff0000u;   // column 0 (log-density) is not a colour feature
-        t.a[0 * kRows + row] = sh_lo;
-        t.a[1 * kRows + row] = sh_hi;
-        t.a[2 * kRows + row] = make_uint4(g0, pack_half2(v[2], v[3]), pack_half2(v[4], v[5]), pack_half2(v[6], v[7]));
-        t.a[3 * kRows + row] = make_uint4(pack_half2(v[8], v[9]), pack_half2(v[10], v[11]), pack_half2(v[12], v[13]), pack_half2(v[14], v[15]));
-    }
-    layer_mma(t, row, wm.c0, 64, 32);
-    relu_row_to_a(t, row);
+    layer_ts(t, row, kColH, wm.sl, 16, 64);
+    sigma = sigma_and_color_input(t.tmem + kColD, t.tmem + kColH, density_scale, sh_lo, sh_hi);
+    layer_ts(t, row, kColH, wm.c0, 64, 32);
+    relu_row_ts(t);
     for (uint32_t k = 0; k < nh_color; k++) {
-        layer_mma(t, row, wm.ch + k * 8 * 64 * 16, 64, 64);
-        relu_row_to_a(t, row);
+        layer_ts(t, row, kColH, wm.ch + k * 8 * 64 * 16, 64, 64);
+        relu_row_ts(t);
     }
-    layer_mma(t, row, wm.cl, 16, 64);
-    {
-        float v[4];
-        tmem_ld4(t.tmem, v);
-        const float h0 = __half2float(__float2half_rn(v[0])), h1 = __half2float(__float2half_rn(v[1])), h2 = __half2float(__float2half_rn(v[2]));
-        r = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h0))));
-        g = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h1))));
-        b = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h2))));
-    }
+    layer_ts(t, row, kColH, wm.cl, 16, 64);
+    rgb_from_acc(t.tmem + kColD, r, g, b);
 }
 
 // The density net alone for the 128 rows of one warpgroup (NeRFNetwork.density, network_ff.py:76-89).  Same precondition as
@@ -245,110 +319,16 @@ __device__ __forceinline__ void mlp_tile128(Tile &t, int row, uint32_t nh_sigma,
 // h[1..15] = geo_feat).
 __device__ __forceinline__ void sigma_tile128(Tile &t, int row, uint32_t nh_sigma, float (&h)[16]) {
     const WeightMap wm = weight_map(nh_sigma, 0);
-    layer_mma(t, row, wm.s0, 64, 32);
-    relu_row_to_a(t, row);
+    layer_ts(t, row, kColE, wm.s0, 64, 32);
+    relu_row_ts(t);
     for (uint32_t k = 0; k < nh_sigma; k++) {
-        layer_mma(t, row, wm.sh + k * 8 * 64 * 16, 64, 64);
-        relu_row_to_a(t, row);
+        layer_ts(t, row, kColH, wm.sh + k * 8 * 64 * 16, 64, 64);
+        relu_row_ts(t);
     }
-    layer_mma(t, row, wm.sl, 16, 64);
-    tmem_ld16(t.tmem, h);
+    layer_ts(t, row, kColH, wm.sl, 16, 64);
+    tmem_ld16(t.tmem + kColD, h);
 #pragma unroll
     for (int i = 0; i < 16; i++) h[i] = __half2float(__float2half_rn(h[i]));
-}
-
-// ---- pipelined variant: issue and completion of a layer are split, so that the caller can do independent work (the next pass's
-//      gather) while the tensor core runs and while the other warps of the group catch up.  No thread waits at a barrier:
-//        every warp     : stores its rows, fence.proxy.async, then ONE arrive on `aready` (count 4)
-//        thread 0       : waits for `aready`, issues the MMAs, commits to `mbar`
-//        every thread   : ... independent work ..., then waits for `mbar` (normally already complete)
-__device__ __forceinline__ void layer_issue(Tile &t, int row, int lane, uint32_t a_saddr, uint32_t w_off, uint32_t N, uint32_t K) {
-    fence_async_smem();      // this thread's A-row stores -> visible to the tensor core's (async proxy) reads
-    fence_before_sync();     // this thread's tcgen05.ld of the previous accumulators are ordered before the arrive
-    __syncwarp();
-#ifdef NGP_LAST_ARRIVER
-    // the LAST of the four warps to arrive issues the layer: nobody waits for the operand, and the issue happens the moment the
-    // operand is complete.  `aready` is a plain 32-bit arrival counter here (acq_rel at CTA scope: the other warps' stores and
-    // proxy fences happen-before the issuer's MMAs).
-    (void)row;
-    if (lane == 0) {
-        uint32_t old;
-        asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(t.aready_saddr) : "memory");
-        if ((old & 3u) == 3u) {
-            fence_after_sync();
-            const uint32_t idesc = instr_desc(N);
-            const uint32_t tmem_d = t.tmem & 0x0000FFFFu;
-            for (uint32_t k = 0; k < K / 16; k++) {
-                const uint64_t ad = smem_desc(a_saddr + k * 2 * (kRows * 16), kRows * 16, 128);
-                const uint64_t bd = smem_desc(t.w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
-                mma_f16_ss(tmem_d, ad, bd, idesc, k > 0 ? 1u : 0u);
-            }
-            mma_commit(t.mbar_saddr);
-        }
-    }
-#else
-    if (lane == 0) mbar_arrive(t.aready_saddr);
-    if (row == 0) {
-        mbar_wait(t.aready_saddr, t.parity_a);
-        fence_after_sync();
-        const uint32_t idesc = instr_desc(N);
-        const uint32_t tmem_d = t.tmem & 0x0000FFFFu;
-        for (uint32_t k = 0; k < K / 16; k++) {
-            const uint64_t ad = smem_desc(a_saddr + k * 2 * (kRows * 16), kRows * 16, 128);
-            const uint64_t bd = smem_desc(t.w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
-            mma_f16_ss(tmem_d, ad, bd, idesc, k > 0 ? 1u : 0u);
-        }
-        mma_commit(t.mbar_saddr);
-    }
-    t.parity_a ^= 1u;
-#endif
-    __syncwarp();
-}
-__device__ __forceinline__ void layer_wait(Tile &t) {
-    mbar_wait(t.mbar_saddr, t.parity);
-    t.parity ^= 1u;
-    fence_after_sync();
-}
-
-// As mlp_tile128, with the first layer's A operand in t.e and `between(step)` called after the MMAs of layer `step` (0-based, in
-// evaluation order) have been handed to the tensor core.  `between` must not touch t.a, and may write t.e only for step >= 1.
-template <class Between>
-__device__ __forceinline__ void mlp_tile128_pipelined(Tile &t, int row, int lane, uint32_t nh_sigma, uint32_t nh_color, float density_scale,
-                                                      const uint4 &sh_lo, const uint4 &sh_hi, float &sigma, float &r, float &g, float &b,
-                                                      Between &&between) {
-    const WeightMap wm = weight_map(nh_sigma, nh_color);
-    const int n_sig = 2 + (int)nh_sigma, n_all = n_sig + 2 + (int)nh_color;
-    // one rolled loop over the layers of both nets: whatever `between` does (a gather trip) exists ONCE in the instruction stream
-#pragma unroll 1
-    for (int step = 0; step < n_all; step++) {
-        const bool in_color = step >= n_sig;
-        const int l = in_color ? step - n_sig : step;                           // layer within its net
-        const bool first = l == 0, last = l == (int)(in_color ? nh_color : nh_sigma) + 1;
-        const uint32_t w_off = (in_color ? wm.c0 : wm.s0) + (first ? 0u : 4096u + (uint32_t)(l - 1) * 8192u);   // [32->64] is 4 KB, [64->64] 8 KB
-        layer_issue(t, row, lane, step == 0 ? t.e_saddr : t.a_saddr, w_off, last ? 16u : 64u, first ? 32u : 64u);
-        between(step);
-        layer_wait(t);
-        if (!last) {
-            relu_row_to_a(t, row);
-        } else if (!in_color) {
-            float v[16];
-            tmem_ld16(t.tmem, v);
-            uint32_t g0 = pack_half2(v[0], v[1]);
-            sigma = expf(__half2float(__ushort_as_half((unsigned short)(g0 & 0xffffu)))) * density_scale;
-            g0 &= 0xffff0000u;   // column 0 (log-density) is not a colour feature
-            t.a[0 * kRows + row] = sh_lo;
-            t.a[1 * kRows + row] = sh_hi;
-            t.a[2 * kRows + row] = make_uint4(g0, pack_half2(v[2], v[3]), pack_half2(v[4], v[5]), pack_half2(v[6], v[7]));
-            t.a[3 * kRows + row] = make_uint4(pack_half2(v[8], v[9]), pack_half2(v[10], v[11]), pack_half2(v[12], v[13]), pack_half2(v[14], v[15]));
-        } else {
-            float v[4];
-            tmem_ld4(t.tmem, v);
-            const float h0 = __half2float(__float2half_rn(v[0])), h1 = __half2float(__float2half_rn(v[1])), h2 = __half2float(__float2half_rn(v[2]));
-            r = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h0))));
-            g = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h1))));
-            b = __half2float(__float2half_rn(__fdividef(1.0f, 1.0f + __expf(-h2))));
-        }
-    }
 }
 
 }  // namespace tc

@@ -68,12 +68,24 @@ class FFMLP(nn.Module):
         std = math.sqrt(3 / self.hidden_dim)
         self.weights.data.uniform_(-std, std)
 
-    def half_weights(self):
+    def half_weights(self, fingerprint=None):
+        """fp16 copy of `weights`, re-cast when the parameter was modified (see GridEncoder.half_table for the key)."""
         w = self.weights
-        key = (w._version, w.data_ptr())
+        key = (w._version, w.data_ptr(), _cabi.fingerprint(w) if fingerprint is None else fingerprint)
         if self._half is None or self._half[0] != key:
             self._half = (key, w.detach().to(torch.half).contiguous())
         return self._half[1]
+
+    def invalidate_caches(self):
+        self._half = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self.invalidate_caches()
+        return super()._load_from_state_dict(*args, **kwargs)
+
+    def _apply(self, fn, *args, **kwargs):
+        self.invalidate_caches()
+        return super()._apply(fn, *args, **kwargs)
 
     def forward(self, inputs):
         B, C = inputs.shape

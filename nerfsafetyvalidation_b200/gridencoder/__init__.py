@@ -89,13 +89,26 @@ class GridEncoder(nn.Module):
                 f"per_level_scale={self.per_level_scale:.4f} params={tuple(self.embeddings.shape)} gridtype={self.gridtype} "
                 f"align_corners={self.align_corners}")
 
-    def half_table(self):
-        """fp16 copy of `embeddings`, re-cast only when the parameter was modified or moved."""
+    def half_table(self, fingerprint=None):
+        """fp16 copy of `embeddings` (the reference re-casts 46.7 MB per call, grid.py:38-39), re-cast only when the parameter
+        was modified or moved.  Writes through `.data` do not bump `_version`, so the key also carries a content fingerprint
+        (_cabi.fingerprint: 32 sampled elements; the caller may pass one it computed for several tensors in a single read-back)."""
         e = self.embeddings
-        key = (e._version, e.data_ptr())
+        key = (e._version, e.data_ptr(), _cabi.fingerprint(e) if fingerprint is None else fingerprint)
         if self._half is None or self._half[0] != key:
             self._half = (key, e.detach().to(torch.half).contiguous())
         return self._half[1]
+
+    def invalidate_caches(self):
+        self._half = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self.invalidate_caches()
+        return super()._load_from_state_dict(*args, **kwargs)
+
+    def _apply(self, fn, *args, **kwargs):
+        self.invalidate_caches()
+        return super()._apply(fn, *args, **kwargs)
 
     def forward(self, inputs, bound=1):
         inputs = (inputs + bound) / (2 * bound)  # grid.py:144

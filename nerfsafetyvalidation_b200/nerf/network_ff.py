@@ -51,23 +51,36 @@ class NeRFNetwork(NeRFRenderer):
         if not self._fusable() or not self.encoder.embeddings.is_cuda:
             return False
         lib = _cabi.load()
-        table = self.encoder.half_table()
-        ws, wc = self.sigma_net.half_weights(), self.color_net.half_weights()
+        fp = _cabi.fingerprint(self.encoder.embeddings, self.sigma_net.weights, self.color_net.weights)   # one read-back for all three
+        table = self.encoder.half_table(fp)
+        ws, wc = self.sigma_net.half_weights(fp), self.color_net.half_weights(fp)
         key = (table.data_ptr(), ws.data_ptr(), wc.data_ptr(), self.encoder.embeddings._version, self.sigma_net.weights._version,
-               self.color_net.weights._version, float(self.bound), float(self.density_scale))
+               self.color_net.weights._version, fp, float(self.bound), float(self.density_scale))
+        dev = table.device
+        handle = owner.get(dev)   # re-created (keys cleared) if the model moved to another device
         if owner.keys is not None and owner.keys.get("net") == key:
             return True
-        handle = owner.get()
         offs_host = self.encoder.offsets.detach().cpu().numpy().astype(np.int32)
         offs_dev = self.encoder.offsets.int().contiguous()
         S = float(np.log2(self.encoder.per_level_scale))
-        _cabi.check(lib.ngp_ctx_set_network(handle, _cabi.ptr(table), _cabi.ptr(offs_dev), offs_host.ctypes.data_as(C.c_void_p),
-                                            self.encoder.num_levels, S, int(self.encoder.base_resolution), _cabi.ptr(ws),
-                                            self.num_layers, _cabi.ptr(wc), self.num_layers_color, float(self.bound),
-                                            float(self.density_scale), _cabi.stream()), "ngp_ctx_set_network")
+        with torch.cuda.device(dev):
+            _cabi.check(lib.ngp_ctx_set_network(handle, _cabi.ptr(table), _cabi.ptr(offs_dev), offs_host.ctypes.data_as(C.c_void_p),
+                                                self.encoder.num_levels, S, int(self.encoder.base_resolution), _cabi.ptr(ws),
+                                                self.num_layers, _cabi.ptr(wc), self.num_layers_color, float(self.bound),
+                                                float(self.density_scale), _cabi.stream()), "ngp_ctx_set_network")
         owner.keys = dict(owner.keys or {}, net=key)
         owner.keep = (table, ws, wc, offs_dev)
         return True
+
+    def invalidate_caches(self):
+        """Drops the fp16 casts of the table and both MLPs and the native context's view of them.  Called automatically by
+        load_state_dict / .to() / .cuda(); call it by hand after writing parameters in a way autograd does not see AND the
+        32-element content fingerprint could miss (e.g. a sparse `.data` update)."""
+        for m in (self.encoder, self.sigma_net, self.color_net):
+            if hasattr(m, "invalidate_caches"):
+                m.invalidate_caches()
+        if self._native.keys:
+            self._native.keys.pop("net", None)
 
     def forward(self, x, d):
         """network_ff.py:51-74: x [N,3] in [-bound,bound], d [N,3] -> (sigma [N] fp32, rgb [N,3]).
@@ -82,8 +95,9 @@ class NeRFNetwork(NeRFRenderer):
             rgb = torch.empty(M, 3, dtype=torch.float32, device=x.device)
             # both MLPs on tcgen05 (128-row tiles, TMEM accumulators) unless the mma.sync formulation is asked for; same results
             fn = lib.ngp_network_forward if getattr(self, "mlp_engine", "tcgen05") == "mma_sync" else lib.ngp_network_forward_tc
-            _cabi.check(fn(self._native.get(), _cabi.ptr(x), _cabi.ptr(d), M, 0, _cabi.ptr(sig), _cabi.ptr(rgb), _cabi.stream()),
-                        "ngp_network_forward")
+            with torch.cuda.device(x.device):
+                _cabi.check(fn(self._native.get(x.device), _cabi.ptr(x), _cabi.ptr(d), M, 0, _cabi.ptr(sig), _cabi.ptr(rgb), _cabi.stream()),
+                            "ngp_network_forward")
             return sig, rgb
         return self._forward_unfused(x, d)
 
@@ -109,8 +123,9 @@ class NeRFNetwork(NeRFRenderer):
             M = x.shape[0]
             sigma = torch.empty(M, dtype=torch.float32, device=x.device)
             geo = torch.empty(M, self.geo_feat_dim, dtype=torch.float16, device=x.device)
-            _cabi.check(_cabi.load().ngp_density_forward(self._native.get(), _cabi.ptr(x), M, 0, _cabi.ptr(sigma), _cabi.ptr(geo),
-                                                         _cabi.stream()), "ngp_density_forward")
+            with torch.cuda.device(x.device):
+                _cabi.check(_cabi.load().ngp_density_forward(self._native.get(x.device), _cabi.ptr(x), M, 0, _cabi.ptr(sigma), _cabi.ptr(geo),
+                                                             _cabi.stream()), "ngp_density_forward")
             return {"sigma": sigma.view(*prefix), "geo_feat": geo.view(*prefix, self.geo_feat_dim)}
         x = self.encoder(x, bound=self.bound)
         h = self.sigma_net(x)

@@ -29,16 +29,40 @@ class _NativeCtx:
 
     def __init__(self):
         self.handle = None
+        self.device = None    # CUDA device index the context (and its workspace) lives on
         self.keys = None      # what the context was last configured with
         self.keep = None      # tensors the context borrows
+        self.options = {}     # ngp_ctx_set_option values, re-applied when the context is re-created
 
-    def get(self):
+    def get(self, device=None):
+        """The context for `device` (a torch.device / index; default: the current device).  A context is bound to the device it
+        was created on (its workspace is allocated there), so a model that moved gets a new one."""
+        import torch
+        dev = torch.cuda.current_device() if device is None else torch.device(device).index
+        if dev is None:
+            dev = torch.cuda.current_device()
+        if self.handle is not None and self.device != dev:
+            self.close()
         if self.handle is None:
             lib = _cabi.load()
             h = C.c_void_p()
-            _cabi.check(lib.ngp_ctx_create(C.byref(h)), "ngp_ctx_create")
-            self.handle = h
+            with torch.cuda.device(dev):
+                _cabi.check(lib.ngp_ctx_create(C.byref(h)), "ngp_ctx_create")
+            self.handle, self.device, self.keys, self.keep = h, dev, None, None
+            for k, v in self.options.items():
+                _cabi.check(lib.ngp_ctx_set_option(h, k.encode(), int(v)), "ngp_ctx_set_option")
         return self.handle
+
+    def set_option(self, name, value):
+        """Epoch-policy tunables of the fused renderer (include/ngp_b200.h: ngp_ctx_set_option); no option changes any output."""
+        self.options[name] = int(value)
+        if self.handle is not None:
+            _cabi.check(_cabi.load().ngp_ctx_set_option(self.handle, name.encode(), int(value)), "ngp_ctx_set_option")
+
+    def close(self):
+        if self.handle is not None:
+            _cabi.load().ngp_ctx_destroy(self.handle)
+        self.handle, self.device, self.keys, self.keep = None, None, None, None
 
     def __deepcopy__(self, memo):
         return _NativeCtx()
@@ -47,13 +71,11 @@ class _NativeCtx:
         return {}
 
     def __setstate__(self, state):
-        self.handle, self.keys, self.keep = None, None, None
+        self.handle, self.device, self.keys, self.keep, self.options = None, None, None, None, {}
 
     def __del__(self):
         try:
-            if self.handle is not None:
-                _cabi.load().ngp_ctx_destroy(self.handle)
-                self.handle = None
+            self.close()
         except Exception:
             pass
 
@@ -225,16 +247,17 @@ class NeRFRenderer(nn.Module):
 
     def _run_fused(self, rays_o, rays_d, prefix, N, device, dt_gamma, max_steps, bg_color, return_stats):
         lib = _cabi.load()
-        handle = self._native.get()
-        self._set_scene(self._native, handle)
         image = torch.empty(N, 3, dtype=torch.float32, device=device)
         depth = torch.empty(N, dtype=torch.float32, device=device)
         weights_sum = torch.empty(N, dtype=torch.float32, device=device)
         spr = torch.empty(N, dtype=torch.int32, device=device) if return_stats else None
         stats = torch.zeros(4, dtype=torch.int64, device=device) if return_stats else None
-        _cabi.check(lib.ngp_render(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
-                                   _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(spr), _cabi.ptr(stats),
-                                   _cabi.stream()), "ngp_render")
+        with torch.cuda.device(device):   # the context, its workspace and the launch stream all belong to the tensors' device
+            handle = self._native.get(device)
+            self._set_scene(self._native, handle)
+            _cabi.check(lib.ngp_render(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
+                                       _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(spr), _cabi.ptr(stats),
+                                       _cabi.stream()), "ngp_render")
         results = {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum,
                    # the reference returns the LAST iteration's per-sample tensors (renderer.py:381-382); the fused loop
                    # never materialises them
@@ -325,11 +348,13 @@ class NeRFRenderer(nn.Module):
             if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous() or tuple(t.shape) != shape:
                 raise RuntimeError(f"render_poses_host: output buffers must be contiguous CPU float32 {shape}")
         lib = _cabi.load()
-        handle = self._native.get()
-        self._set_scene(self._native, handle)
         fx, fy, cx, cy = (float(v) for v in intrinsics)
-        _cabi.check(lib.ngp_render_poses_host(handle, _cabi.ptr(poses), F, H, W, fx, fy, cx, cy, float(dt_gamma), int(max_steps),
-                                              float(bg_color), _cabi.ptr(image), _cabi.ptr(depth), _cabi.stream()), "ngp_render_poses_host")
+        dev = self.density_bitfield.device
+        with torch.cuda.device(dev):
+            handle = self._native.get(dev)
+            self._set_scene(self._native, handle)
+            _cabi.check(lib.ngp_render_poses_host(handle, _cabi.ptr(poses), F, H, W, fx, fy, cx, cy, float(dt_gamma), int(max_steps),
+                                                  float(bg_color), _cabi.ptr(image), _cabi.ptr(depth), _cabi.stream()), "ngp_render_poses_host")
         return image, depth
 
     @torch.no_grad()

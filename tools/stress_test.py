@@ -39,7 +39,7 @@ def main():
     if world > 1:   # replicated weights: ONE broadcast per tensor at start-up
         for t in (model.encoder.embeddings.data, model.sigma_net.weights.data, model.color_net.weights.data, model.density_bitfield):
             dist.broadcast(t, src=0)
-        model.encoder._half = model.sigma_net._half = model.color_net._half = None
+        model.invalidate_caches()
     focal = 277.78 * args.res / 200
     kw = dict(rank=rank, world=world, frames_per_call=args.frames_per_call)
     ro.monte_carlo(model, world * 4, 2, args.res, args.res, focal, **kw)   # warm-up

@@ -79,6 +79,8 @@ def parse():
     p.add_argument("--split-rows", action="store_true",
                    help="single-frame workloads under torchrun: ONE frame, rank r renders the r-th block of image rows (strong scaling; "
                         "SURVEY section 8d cfg5) instead of one frame per rank")
+    p.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                   help="ngp_ctx_set_option tunable of the renderer's epoch policy (e.g. rows_per_ray=64); recorded in config.options")
     return p.parse_args()
 
 
@@ -265,6 +267,9 @@ def main():
             dist.broadcast(t, src=0)
         model.invalidate_caches()
     lib = _cabi.load()
+    options = {k: int(v) for k, v in (o.split("=", 1) for o in args.opt)}
+    for k, v in options.items():
+        model._native.set_option(k, v)
 
     n_frames = wl.get("frames", 1)
     split_rows = args.split_rows and world > 1 and n_frames == 1
@@ -376,7 +381,7 @@ def main():
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if split_rows else "weak",
                 "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
                 "config": {"workload": wl["desc"], "variant": args.variant, "rays_per_gpu_per_step": N, "samples_per_step": samples,
-                           "samples_per_ray": samples / N, "iterations_per_step": iters, "epochs_per_step": epochs, "replayed_epochs": replays,
+                           "samples_per_ray": samples / N, "iterations_per_step": iters, "epochs_per_step": epochs, "replayed_epochs": replays, **({"options": options} if options else {}),
                            "frames_per_step": n_frames,
                            "l2": "flushed between steps (256 MB write)", "parallelism": f"replicated weights, {world} ray shards" + (" (row blocks of ONE frame)" if split_rows else "")},
                 "frames_per_s": n_frames * (1 if split_rows else world) / (ms_step * 1e-3), "msamples_per_s": samples_all / (ms_step * 1e-3) / 1e6,

@@ -316,23 +316,23 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
                                                             float *__restrict__ sigmas, void *__restrict__ rgbs_or_geo, uint32_t n_tiles) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
-    uint64_t *s_mbar = reinterpret_cast<uint64_t *>(s_w + nc.wtc_bytes / 16);
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_mbar + 1);
-    const int tid = threadIdx.x, warp = tid >> 5;
+    uint64_t *s_mbar = reinterpret_cast<uint64_t *>(s_w + nc.wtc_bytes / 16);   // one per warp
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_mbar + 4);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (uint32_t i = tid; i < nc.wtc_bytes / 16; i += blockDim.x) s_w[i] = __ldg(nc.wtc + i);
     tc::fence_async_smem();
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(s_tmem), tc::kTmemColsTs);
     if (tid == 0) {
-        tc::mbar_init(tc::smem_u32(s_mbar), 1);
+        for (int i = 0; i < 4; i++) tc::mbar_init(tc::smem_u32(s_mbar + i), 1);
         tc::mbar_init_fence();
     }
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(s_tmem);
-    tc::Tile t;
-    t.w_saddr = tc::smem_u32(s_w); t.mbar_saddr = tc::smem_u32(s_mbar);
-    t.tmem = tmem_base + ((uint32_t)(warp * 32) << 16); t.bar_id = 1; t.parity = 0;
+    tc::Tile t;   // the four warps run independent chains on their own lane quadrant of the tile
+    t.w_saddr = tc::smem_u32(s_w); t.mbar_saddr = tc::smem_u32(s_mbar + warp);
+    t.tmem = tmem_base + ((uint32_t)(warp * 32) << 16); t.q = warp; t.parity = 0;
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint32_t row = tile * tc::kRows + tid;
         uint4 sh_lo = make_uint4(0, 0, 0, 0), sh_hi = sh_lo;
@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
         encode_point_tmem<4>(nc, x, y, z, row < M, t.tmem + tc::kColE);
         if (kDensityOnly) {
             float h[16];
-            tc::sigma_tile128(t, tid, nc.nh_sigma, h);
+            tc::sigma_tile128(t, lane, nc.nh_sigma, h);
             if (row < M) {
                 sigmas[row] = expf(h[0]) * nc.density_scale;   // trunc_exp of the half output, in fp32 (activation.py:5-18)
                 if (rgbs_or_geo) {
@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(128) k_network_forward_tc(NetConst nc, const f
             }
         } else {
             float sg, r, g, b;
-            tc::mlp_tile128(t, tid, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, r, g, b);
+            tc::mlp_tile128(t, lane, nc.nh_sigma, nc.nh_color, nc.density_scale, sh_lo, sh_hi, sg, r, g, b);
             if (row < M) {
                 sigmas[row] = sg;
                 float *o = reinterpret_cast<float *>(rgbs_or_geo) + (size_t)row * 3;
@@ -437,13 +437,15 @@ constexpr int kMaxEpoch = 128;                 // reference iterations per epoch
 #define NGP_MAX_SAMPLES_PER_EPOCH 128
 #endif
 constexpr int kMaxSamplesPerEpoch = NGP_MAX_SAMPLES_PER_EPOCH;      // E * s cap: bounds the longest tile of an epoch
+constexpr int kScratchPerWarp = 32 * (2 + 3);   // float4 per epilogue warp: compositing scratch (2 per lane) + ray state (3 per lane)
+constexpr uint32_t kTilesPerTicket = 1;      // EVALUATE: consecutive 32-row warp tiles (adjacent rays: shared hash-grid cells) per claimed ticket
 constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
 
 struct EpochCtr {
     uint32_t cursor;            // MARCH phase: next unclaimed entry of the live list
     uint32_t ticket;            // EVALUATE phase: next unclaimed 128-row stream tile
     uint32_t n_out;             // survivors appended to the next live list
-    uint32_t opaque;            // some ray of this epoch ended with weights_sum > 0.9: transmittance deaths are near
+    uint32_t opaque;            // bits of the largest weights_sum any surviving ray ended this epoch with (a float in [0, 1): orders like its bits)
     uint32_t hist[kMaxEpoch];   // rays that died in iteration j of the epoch
     uint32_t mhist[kMaxEpoch];  // of those, the ones that ran out of samples -- known to the marcher, before anything is evaluated
 };
@@ -455,7 +457,7 @@ struct RenderCtr {
 
 // Tunables of the epoch policy (ngp_ctx_set_option); the defaults are what every committed number was measured with.
 struct RenderOptions {
-    uint32_t rows_per_ray = 32;   // sample-buffer rows per ray (one epoch's samples of every live ray must fit)
+    uint32_t rows_per_ray = 64;   // sample-buffer rows per ray (one epoch's samples of every live ray must fit); 8 B each
     uint32_t max_epoch = 0;       // cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t kshift = 4;          // >= 4: automatic; else log2 of the samples per ray per evaluation pass
     uint32_t t_div = 2;           // once rays die by transmittance: E = margin / (t_div * rate)
@@ -463,6 +465,9 @@ struct RenderOptions {
     uint32_t e0_cap = 4;          // cap on E of the first epoch (0 = none)
     uint32_t rate0_div = 128;     // death-rate prior of the first epochs: N / rate0_div + 1 per iteration
     uint32_t no_coarse = 0;       // 1 = do not build / use the coarse occupancy grid
+    uint32_t early_cap = 32;      // samples per epoch until every ray has had `early_steps` samples (0 = off, the default: the
+    uint32_t early_steps = 0;     //   transmittance horizon below decides how long an epoch dares to be)
+    uint32_t horizon_div = 2;     // an epoch spends at most 1 / horizon_div of the samples left before the first extrapolated T < 1e-4
 };
 
 struct RenderArgs {
@@ -489,6 +494,8 @@ struct RenderArgs {
     uint32_t cap_n[kMaxStep], cap_t[kMaxStep];
     uint32_t e0_cap;         // cap on E of the first epoch (0 = none): a short probe epoch learns cheaply whether rays die by transmittance
     uint32_t rate0;          // death-rate prior for the first epochs: N / 128 + 1 deaths per iteration
+    uint32_t early_cap, early_steps;   // E * s <= early_cap while step < early_steps (RenderOptions)
+    float horizon_div;                 // epochs use at most 1 / horizon_div of the samples left before the first transmittance death
     RenderCtr *ctr;
     float *image, *depth, *weights_sum;
     int *samples_per_ray;
@@ -576,141 +583,156 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
     }
 }
 
-// ---- EVALUATE: the per-stream pipeline state in shared memory
-struct __align__(16) StreamSync {
-    uint64_t dfull;      // mbarrier, count 1: tcgen05.commit of every layer -- the accumulators D are complete
+// ---- EVALUATE: the pipeline state of one PAIR (gather warp + epilogue warp on the same lane quadrant of the same TMEM columns)
+struct __align__(16) PairSync {
+    uint64_t dfull;      // mbarrier, count 1: tcgen05.commit of every layer -- this quadrant's accumulators D are complete
     uint64_t empty[2];   // mbarrier, count 1: tcgen05.commit of layer 0 -- the E slot has been consumed (pre-armed once)
-    uint32_t cnt_e[2];   // per E slot: 4 gather-warp arrivals (the slot is filled) + 4 epilogue-warp arrivals (the previous pass has
-                         // let go of D); whoever brings it to 0 mod 8 issues layer 0 -- nobody waits for the other side
-    uint32_t cnt_h;      // epilogue-warp arrivals per layer (the warp that brings it to 0 mod 4 issues the next layer)
-    uint32_t ticket[2];  // the stream's current / next tile, claimed from EpochCtr::ticket by the team leader (gather warp 0) ...
-    uint32_t pad;
-    uint64_t tfull[2];   // ... mbarrier, count 1: the ticket is published
-    uint64_t tempty[2];  // ... mbarrier, count 7: the other seven warps of the stream have read it (pre-armed once)
-    unsigned long long dead[4];   // per lane quadrant: (tile + 1) << 32 | lanes whose ray has terminated -- a hint for the gather
+    uint64_t tfull[2];   // mbarrier, count 1: the gather warp has published the pair's next tile ...
+    uint64_t tempty[2];  // mbarrier, count 1: ... and the epilogue warp has read it (pre-armed once)
+    uint32_t cnt_e[2];   // per E slot: one arrival of the gather warp (the slot is filled) + one of the epilogue warp (the previous pass
+                         // has let go of D); whoever makes the second issues layer 0 -- neither waits for the other
+    uint32_t ticket[2];  // the pair's current / next warp tile, claimed from EpochCtr::ticket
+    unsigned long long dead;   // (tile + 1) << 32 | lanes whose ray has terminated -- a hint for the gather warp
 };
-__device__ __forceinline__ void stream_sync_init(StreamSync &ss) {   // one thread
-    tc::mbar_init(tc::smem_u32(&ss.dfull), 1);
-    tc::mbar_init(tc::smem_u32(&ss.empty[0]), 1);
-    tc::mbar_init(tc::smem_u32(&ss.empty[1]), 1);
-    ss.cnt_e[0] = 4u;   // D is free before the first pass: the four epilogue arrivals of slot 0 are pre-paid
-    ss.cnt_e[1] = ss.cnt_h = 0;
+__device__ __forceinline__ void pair_sync_init(PairSync &ps) {   // one thread
+    tc::mbar_init(tc::smem_u32(&ps.dfull), 1);
     for (int i = 0; i < 2; i++) {
-        tc::mbar_init(tc::smem_u32(&ss.tfull[i]), 1);
-        tc::mbar_init(tc::smem_u32(&ss.tempty[i]), 7);
+        tc::mbar_init(tc::smem_u32(&ps.empty[i]), 1);
+        tc::mbar_init(tc::smem_u32(&ps.tfull[i]), 1);
+        tc::mbar_init(tc::smem_u32(&ps.tempty[i]), 1);
     }
-    ss.dead[0] = ss.dead[1] = ss.dead[2] = ss.dead[3] = 0ull;
+    ps.cnt_e[0] = 1u;   // D is free before the first pass: the epilogue arrival of slot 0 is pre-paid
+    ps.cnt_e[1] = 0u;
+    ps.dead = 0ull;
 }
-__device__ __forceinline__ void stream_sync_prearm(StreamSync &ss) {   // one thread, after the init fence: phase 0 of "free" is complete
-    for (int i = 0; i < 7; i++) {
-        tc::mbar_arrive(tc::smem_u32(&ss.tempty[0]));
-        tc::mbar_arrive(tc::smem_u32(&ss.tempty[1]));
+__device__ __forceinline__ void pair_sync_prearm(PairSync &ps) {   // one thread, after the init fence: phase 0 of every "free" barrier is complete
+    for (int i = 0; i < 2; i++) {
+        tc::mbar_arrive(tc::smem_u32(&ps.tempty[i]));
+        tc::mbar_arrive(tc::smem_u32(&ps.empty[i]));
     }
-    tc::mbar_arrive(tc::smem_u32(&ss.empty[0]));
-    tc::mbar_arrive(tc::smem_u32(&ss.empty[1]));
-}
-
-// Rays and pass count of one 128-row stream tile, computed identically by the gather and the epilogue team (the two never
-// exchange anything but barrier arrivals): has_ray / n / ne of this lane's ray in warp tile 4 gtile + q, and the longest ray of
-// the four warp tiles.
-struct TileRays {
-    uint32_t n, ne, max_ne;
-    bool has_ray;
-};
-__device__ __forceinline__ TileRays tile_rays(const RenderArgs &ra, uint32_t gtile, int q, uint32_t my_r, uint32_t R, uint32_t n_alive, uint32_t ES) {
-    TileRays tr;
-    tr.ne = 0; tr.max_ne = 0;
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-        const uint32_t nj = (gtile * 4u + (uint32_t)j) * R + my_r;
-        const uint32_t e = nj < n_alive ? min(__ldcg(ra.n_emit + nj), ES) : 0u;   // ES may be shorter than what was marched (pre-validated epoch)
-        tr.max_ne = max(tr.max_ne, e);
-        if (j == q) tr.ne = e;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) tr.max_ne = max(tr.max_ne, __shfl_xor_sync(0xffffffffu, tr.max_ne, o));
-    tr.n = (gtile * 4u + (uint32_t)q) * R + my_r;
-    tr.has_ray = tr.n < n_alive;
-    return tr;
 }
 
-// Dynamic tile scheduling inside a stream.  The eight warps of a stream walk the same sequence of tiles; tile number T of that
-// sequence (counted since the kernel started, like the pass counter) is claimed from the epoch's global ticket counter by the team
-// leader and handed to the other seven through a two-deep ring: all waits sleep in hardware, none polls.
-__device__ __forceinline__ uint32_t ticket_publish(StreamSync &ss, uint32_t *ticket_ctr, uint32_t T, int lane) {   // the leader warp
+// Dynamic tile scheduling.  Both warps of a pair walk the same sequence of 32-row warp tiles; tile number T of that sequence (counted
+// since the kernel started, like the pass counter) is claimed from the epoch's global ticket counter by the gather warp and handed to
+// the epilogue warp through a two-deep ring.  All waits sleep in hardware, none polls.
+__device__ __forceinline__ uint32_t ticket_publish(PairSync &ps, uint32_t *ticket_ctr, uint32_t T, int lane) {   // gather warp
     const uint32_t ts = T & 1u;
-    tc::mbar_wait(tc::smem_u32(&ss.tempty[ts]), (T >> 1) & 1u, 0x40000000u | T);
+    tc::mbar_wait(tc::smem_u32(&ps.tempty[ts]), (T >> 1) & 1u, 0x40000000u | T);
     uint32_t t = 0;
     if (lane == 0) {
         t = atomicAdd(ticket_ctr, 1u);
-        *reinterpret_cast<volatile uint32_t *>(&ss.ticket[ts]) = t;
-        tc::mbar_arrive(tc::smem_u32(&ss.tfull[ts]));   // release: the ticket is visible to whoever sees the phase complete
+        *reinterpret_cast<volatile uint32_t *>(&ps.ticket[ts]) = t;
+        tc::mbar_arrive(tc::smem_u32(&ps.tfull[ts]));   // release: the ticket is visible to whoever sees the phase complete
     }
     return __shfl_sync(0xffffffffu, t, 0);
 }
-__device__ __forceinline__ uint32_t ticket_consume(StreamSync &ss, uint32_t T, int lane) {   // the other seven warps
+__device__ __forceinline__ uint32_t ticket_consume(PairSync &ps, uint32_t T, int lane) {   // epilogue warp
     const uint32_t ts = T & 1u;
-    tc::mbar_wait(tc::smem_u32(&ss.tfull[ts]), (T >> 1) & 1u, 0x50000000u | T);
-    const uint32_t t = *reinterpret_cast<volatile uint32_t *>(&ss.ticket[ts]);
+    tc::mbar_wait(tc::smem_u32(&ps.tfull[ts]), (T >> 1) & 1u, 0x50000000u | T);
+    const uint32_t t = *reinterpret_cast<volatile uint32_t *>(&ps.ticket[ts]);
     __syncwarp();
-    if (lane == 0) tc::mbar_arrive(tc::smem_u32(&ss.tempty[ts]));
+    if (lane == 0) tc::mbar_arrive(tc::smem_u32(&ps.tempty[ts]));
     return t;
 }
 
-// Layer 0 of a pass (A = E slot, 32 -> 64), issued by whichever thread made the eighth arrival on the slot's counter.
-__device__ __forceinline__ void issue_layer0(uint32_t tmem_lane, uint32_t w_saddr, uint32_t slot, uint32_t empty_saddr, uint32_t dfull_saddr) {
+// The MMAs of every layer, prepared once per launch in shared memory: the issuing lane only loads descriptors and fires.
+constexpr int kMaxLayers = 10;   // 2 nets x (first + <= 3 hidden + last)
+struct __align__(16) LayerDesc {
+    uint64_t bdesc[4];   // shared-memory descriptors of the weight K-chunks (16 columns of K each)
+    uint32_t idesc;      // instruction descriptor (N = 64 | 16)
+    uint32_t nk;         // K / 16
+    uint32_t pad[2];
+};
+__device__ __forceinline__ void layer_table_init(LayerDesc *tab, const NetConst &nc, uint32_t w_saddr, int tid) {   // threads 0 .. n_all - 1
+    const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
+    const int n_sig = 2 + (int)nc.nh_sigma, n_all = n_sig + 2 + (int)nc.nh_color;
+    if (tid >= n_all) return;
+    const bool in_color = tid >= n_sig;
+    const int l = in_color ? tid - n_sig : tid;
+    const bool first = l == 0, last = l == (int)(in_color ? nc.nh_color : nc.nh_sigma) + 1;
+    const uint32_t w_off = (in_color ? wm.c0 : wm.s0) + (first ? 0u : 4096u + (uint32_t)(l - 1) * 8192u);   // [32->64] is 4 KB, [64->64] 8 KB
+    const uint32_t N = last ? 16u : 64u, K = first ? 32u : 64u;
+    LayerDesc d;
+    for (uint32_t k = 0; k < 4; k++) d.bdesc[k] = tc::smem_desc(w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
+    d.idesc = tc::instr_desc(N); d.nk = K / 16; d.pad[0] = d.pad[1] = 0;
+    tab[tid] = d;
+}
+// One layer for lane quadrant q: D = A (TMEM columns from tmem_a) x W^T.  One thread.
+__device__ __forceinline__ void issue_layer(const LayerDesc &ld, uint32_t tmem_d, uint32_t tmem_a, int q) {
+    const uint32_t m0 = q == 0 ? 0u : 0xffffffffu, m1 = q == 1 ? 0u : 0xffffffffu, m2 = q == 2 ? 0u : 0xffffffffu, m3 = q == 3 ? 0u : 0xffffffffu;
+    const uint32_t idesc = ld.idesc, nk = ld.nk;
+    tc::mma_f16_ts_masked(tmem_d, tmem_a, ld.bdesc[0], idesc, 0u, m0, m1, m2, m3);
+    tc::mma_f16_ts_masked(tmem_d, tmem_a + 8, ld.bdesc[1], idesc, 1u, m0, m1, m2, m3);
+    if (nk > 2) {
+        tc::mma_f16_ts_masked(tmem_d, tmem_a + 16, ld.bdesc[2], idesc, 1u, m0, m1, m2, m3);
+        tc::mma_f16_ts_masked(tmem_d, tmem_a + 24, ld.bdesc[3], idesc, 1u, m0, m1, m2, m3);
+    }
+}
+
+// Layer 0 of a pass (A = E slot, 32 -> 64) for the pair's lane quadrant, issued by whichever of the two warps made the second arrival
+// on the slot's counter.
+__device__ __forceinline__ void issue_layer0(uint32_t tmem_lane, const LayerDesc *layers, uint32_t slot, int q, uint32_t empty_saddr, uint32_t dfull_saddr) {
     tc::fence_after_sync();
     const uint32_t base = tmem_lane & 0x0000FFFFu;
 #ifndef NGP_ABLATE_MLP
-    tc::issue_layer_ts(base + tc::kColD, base + tc::kColE + slot * 16u, w_saddr, 64, 32);
+    issue_layer(layers[0], base + tc::kColD, base + tc::kColE + slot * 16u, q);
 #endif
     tc::mma_commit(empty_saddr);   // the slot may be refilled ...
-    tc::mma_commit(dfull_saddr);   // ... and the epilogue team may read D once these MMAs have completed
+    tc::mma_commit(dfull_saddr);   // ... and the epilogue warp may read D once these MMAs have completed
 }
 
-// GATHER role of one warp: quadrant q (32 rows) of every pass of every tile of its stream.  P: passes this stream has issued since
-// the kernel started (selects the E slot and the barrier phases; identical in all eight warps of the stream).
+// GATHER role of one warp: every pass of every warp tile the pair claims.  A warp tile is R = 32 / K consecutive live rays; a pass is K
+// consecutive samples of each (lane = r * K + k = TMEM lane within the quadrant).  P / T: passes / tiles this pair has issued since the
+// kernel started (they select the E slot, the ticket slot and the barrier phases; identical in both warps of the pair).
 template <bool kProf>
-__device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs &ra, StreamSync &ss, uint32_t tmem_lane, uint32_t w_saddr, int lane,
+__device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs &ra, PairSync &ps, uint32_t tmem_lane, const LayerDesc *layers, int lane,
                                             int q, uint32_t *ticket_ctr, const int *__restrict__ alive_in, uint32_t n_alive,
                                             uint32_t ES, const TileGeom tg, uint32_t &P, uint32_t &T, long long (&pc)[8]) {
     const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
-    const uint32_t n_tiles = (n_alive + R - 1) / R, n_gtiles = (n_tiles + 3) / 4;
+    const uint32_t n_tiles = (n_alive + R - 1) / R;
     const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
     const uint32_t tile_rows = R * tg.ESp;
-    const uint32_t empty_s = tc::smem_u32(&ss.empty[0]), cnt_s = tc::smem_u32(&ss.cnt_e[0]), dfull_s = tc::smem_u32(&ss.dfull);
-    const volatile unsigned long long *dead_w = &ss.dead[q];
+    const uint32_t ps_s = tc::smem_u32(&ps);   // one base register; the fields are immediate offsets
+    constexpr uint32_t kEmpty = offsetof(PairSync, empty), kCnt = offsetof(PairSync, cnt_e), kDfull = offsetof(PairSync, dfull);
+    const volatile unsigned long long *dead_w = &ps.dead;
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
-    const bool team_leader = q == 0;
-    uint32_t gtile = team_leader ? ticket_publish(ss, ticket_ctr, T, lane) : ticket_consume(ss, T, lane);
+    const uint32_t n_tickets = (n_tiles + kTilesPerTicket - 1) / kTilesPerTicket;
+    uint32_t ticket = ticket_publish(ps, ticket_ctr, T, lane);
     T++;
-    while (gtile < n_gtiles) {
-        uint32_t next_tile = 0;
-        if (team_leader) next_tile = ticket_publish(ss, ticket_ctr, T, lane);   // one tile ahead: the claim's latency hides behind this tile
-        const TileRays tr = tile_rays(ra, gtile, q, my_r, R, n_alive, ES);
+    while (ticket < n_tickets) {
+      const uint32_t next_ticket = ticket_publish(ps, ticket_ctr, T, lane);   // one ahead: the claim's latency hides behind these tiles
+      T++;
+      for (uint32_t tile = ticket * kTilesPerTicket; tile < min(n_tiles, (ticket + 1u) * kTilesPerTicket); tile++) {
+        const uint32_t n = tile * R + my_r;
+        const bool has_ray = n < n_alive;
+        uint32_t ne = 0;
         float ox = 0.f, oy = 0.f, oz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
-        if (tr.has_ray) {
-            const int index = __ldcg(alive_in + tr.n);
+        if (has_ray) {
+            ne = min(__ldcg(ra.n_emit + n), ES);   // ES may be shorter than what was marched (pre-validated epoch)
+            const int index = __ldcg(alive_in + n);
             const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
             ox = __ldg(o); oy = __ldg(o + 1); oz = __ldg(o + 2);
             dx = __ldg(d); dy = __ldg(d + 1); dz = __ldg(d + 2);
         }
-        const uint32_t tbase = (gtile * 4u + (uint32_t)q) * tile_rows + (uint32_t)lane;
+        uint32_t max_ne = ne;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) max_ne = max(max_ne, __shfl_xor_sync(0xffffffffu, max_ne, o));
+        const uint32_t tbase = tile * tile_rows + (uint32_t)lane;
         float t_next = 0.f;
-        if (my_k < tr.ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase));
+        if (my_k < ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase));
         NGP_PROF(0)
-        for (uint32_t i0 = 0; i0 < tr.max_ne; i0 += K, P++) {
+        for (uint32_t i0 = 0; i0 < max_ne; i0 += K, P++) {
             const uint32_t slot = P & 1u;
-            tc::mbar_wait(empty_s + slot * 8u, (P >> 1) & 1u, 0x10000000u | P);   // layer 0 of pass P - 2 has consumed this slot
+            tc::mbar_wait(ps_s + kEmpty + slot * 8u, (P >> 1) & 1u, 0x10000000u | P);   // layer 0 of pass P - 2 has consumed this slot
             tc::fence_after_sync();
             NGP_PROF(5)
             const uint32_t i = i0 + my_k;
             const unsigned long long dw = *dead_w;
-            const bool dead = (uint32_t)(dw >> 32) == gtile + 1u && (((uint32_t)dw >> lane) & 1u);
-            const bool active = tr.has_ray && i < tr.ne && !dead;
+            const bool dead = (uint32_t)(dw >> 32) == tile + 1u && (((uint32_t)dw >> lane) & 1u);
+            const bool active = has_ray && i < ne && !dead;
             const float t = t_next;
-            if (!dead && i + K < tr.ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase + (i0 + K) * R));
+            if (!dead && i + K < ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase + (i0 + K) * R));
 #ifdef NGP_ABLATE_GATHER   // ablation builds (tools/ab_build.sh): what does the frame cost without one of the two big phases?
             const bool gather_on = false;   // the operand is all zeros: deterministic, so the epoch speculation still converges
 #else
@@ -722,68 +744,72 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
             tc::fence_before_sync();
             __syncwarp();
             NGP_PROF(3)
-            if (lane == 0 && (tc::smem_arrive_count(cnt_s + slot * 4u) & 7u) == 7u)   // slot filled AND D free: issue layer 0
-                issue_layer0(tmem_lane, w_saddr, slot, empty_s + slot * 8u, dfull_s);
+            if (lane == 0 && (tc::smem_arrive_count(ps_s + kCnt + slot * 4u) & 1u) == 1u)   // slot filled AND D free: issue layer 0
+                issue_layer0(tmem_lane, layers, slot, q, ps_s + kEmpty + slot * 8u, ps_s + kDfull);
             __syncwarp();
             NGP_PROF(5)
         }
-        if (!team_leader) next_tile = ticket_consume(ss, T, lane);
-        T++;
-        gtile = next_tile;
-        NGP_PROF(5)
+      }
+      ticket = next_ticket;
     }
 #undef NGP_PROF
 }
 
-// EPILOGUE role of one warp: quadrant q of its stream -- every layer's activation, then compositing, ray state and the next live list.
-// par: phase parity of ss.dfull (one phase per layer), persistent like P.
+// EPILOGUE role of one warp: every layer's activation for the pair's 32 rows, then compositing, ray state and the next live list.
+// par: phase parity of ps.dfull (one phase per layer), persistent like P and T.
 template <bool kProf>
-__device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderArgs &ra, StreamSync &ss, uint32_t tmem_lane, uint32_t w_saddr,
+__device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderArgs &ra, PairSync &ps, uint32_t tmem_lane, const LayerDesc *layers,
                                               float4 *scratch, int lane, int q, uint32_t lt_mask,
                                               const int *__restrict__ alive_in, int *__restrict__ alive_out, const float4 *__restrict__ state_in,
                                               float4 *__restrict__ state_out, uint32_t n_alive, uint32_t s, uint32_t ES, const TileGeom tg,
                                               uint32_t seq, EpochCtr *ec, uint32_t *s_hist, uint32_t &P, uint32_t &T, uint32_t &par, long long (&pc)[8]) {
     const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
-    const uint32_t n_tiles = (n_alive + R - 1) / R, n_gtiles = (n_tiles + 3) / 4;
+    const uint32_t n_tiles = (n_alive + R - 1) / R;
     const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
     const bool leader = my_k == 0;
     const int lead_lane = lane & ~(int)(K - 1u);
     const uint32_t tile_rows = R * tg.ESp;
-    const uint32_t dfull_s = tc::smem_u32(&ss.dfull), cnt_s = tc::smem_u32(&ss.cnt_h), cnt_e_s = tc::smem_u32(&ss.cnt_e[0]),
-                   empty_s = tc::smem_u32(&ss.empty[0]);
-    const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
+    const uint32_t ps_s = tc::smem_u32(&ps);   // one base register; the fields are immediate offsets
+    constexpr uint32_t kEmpty = offsetof(PairSync, empty), kCnt = offsetof(PairSync, cnt_e), kDfull = offsetof(PairSync, dfull);
     const int n_sig = 2 + (int)nc.nh_sigma, n_all = n_sig + 2 + (int)nc.nh_color;
     const uint32_t t_d = tmem_lane + tc::kColD, t_h = tmem_lane + tc::kColH, base = tmem_lane & 0x0000FFFFu;
     float4 *scr = scratch + 2 * lane;   // this lane's 32 bytes of its warp's compositing scratch
+    float4 *rs = scratch + 64 + 3 * lane;   // ... and the 48 bytes of ray state behind it
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
-    for (uint32_t gtile = ticket_consume(ss, T++, lane); gtile < n_gtiles; gtile = ticket_consume(ss, T++, lane)) {
-        NGP_PROF(6)
-        const TileRays tr = tile_rays(ra, gtile, q, my_r, R, n_alive, ES);
-        const uint32_t ne = tr.ne;
-        const bool has_ray = tr.has_ray;
+    const uint32_t n_tickets = (n_tiles + kTilesPerTicket - 1) / kTilesPerTicket;
+    for (uint32_t ticket = ticket_consume(ps, T++, lane); ticket < n_tickets; ticket = ticket_consume(ps, T++, lane)) {
+      NGP_PROF(6)
+      for (uint32_t tile = ticket * kTilesPerTicket; tile < min(n_tiles, (ticket + 1u) * kTilesPerTicket); tile++) {
+        const uint32_t n = tile * R + my_r;
+        const bool has_ray = n < n_alive;
+        uint32_t ne = 0;
         int index = 0;
         float dx = 0.f, dy = 0.f, dz = 1.f;
-        RayAcc a = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        uint32_t samples = 0;
+        // The accumulators of a ray live in SHARED memory between passes (3 x 16 B in its leader lane's slot): only the leader lanes touch
+        // them, for a few instructions per pass, and keeping them out of the register file is what keeps the layer loop free of spills.
+        //   rs[0] = (t, weights_sum, depth, samples)   rs[1] = (r, g, b, death)   rs[2] = (chunk, in_chunk, -, -)
         if (has_ray) {
-            index = __ldcg(alive_in + tr.n);
+            ne = min(__ldcg(ra.n_emit + n), ES);
+            index = __ldcg(alive_in + n);
             const float *d = ra.rays_d + (size_t)index * 3;
             dx = __ldg(d); dy = __ldg(d + 1); dz = __ldg(d + 2);   // the direction is constant along the ray: SH per pass from registers
             if (leader) {
                 const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
-                a.t = r0.x; a.ws = r0.y; a.d = r0.z; a.r = r1.x; a.g = r1.y; a.b = r1.z;
-                samples = __float_as_uint(r1.w);
+                rs[0] = make_float4(r0.x, r0.y, r0.z, r1.w);
+                rs[1] = make_float4(r1.x, r1.y, r1.z, 0.f);
+                rs[2] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
         }
-        const uint32_t tbase = (gtile * 4u + (uint32_t)q) * tile_rows + (uint32_t)lane;
+        uint32_t max_ne = ne;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) max_ne = max(max_ne, __shfl_xor_sync(0xffffffffu, max_ne, o));
+        const uint32_t tbase = tile * tile_rows + (uint32_t)lane;
         float2 sn = make_float2(0.f, 0.f);
         if (my_k < ne) sn = __ldcg(ra.smp + tbase);
         bool dead = false;           // the ray of this lane (leader decides, its K lanes follow)
-        uint32_t death = 0;          // leader: iteration of the epoch this ray died in
-        uint32_t chunk = 0, in_chunk = 0;   // leader: position of the next sample in the reference's chunking
         NGP_PROF(0)
-        for (uint32_t i0 = 0; i0 < tr.max_ne; i0 += K, P++) {
+        for (uint32_t i0 = 0; i0 < max_ne; i0 += K, P++) {
             const uint32_t i = i0 + my_k;
             const bool active = has_ray && !dead && i < ne;
             const float2 sc = sn;
@@ -792,7 +818,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
 #ifndef NGP_ABLATE_MLP
 #pragma unroll 1
             for (int step = 0; step < n_all; step++) {
-                tc::mbar_wait(dfull_s, par, 0x30000000u | ((uint32_t)step << 24) | P);
+                tc::mbar_wait(ps_s + kDfull, par, 0x30000000u | ((uint32_t)step << 24) | P);
                 par ^= 1u;
                 tc::fence_after_sync();
                 NGP_PROF(6)
@@ -803,93 +829,90 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                     tc::rgb_from_acc(t_d, cr, cg, cbl);
                     tc::fence_before_sync();
                     __syncwarp();
-                    // D is free: that is one of the eight arrivals layer 0 of the NEXT pass needs; if its slot is already filled, issue it here
+                    // D is free: that is one of the two arrivals layer 0 of the NEXT pass needs; if its slot is already filled, issue it here
                     const uint32_t nslot = (P + 1u) & 1u;
-                    if (lane == 0 && (tc::smem_arrive_count(cnt_e_s + nslot * 4u) & 7u) == 7u)
-                        issue_layer0(tmem_lane, w_saddr, nslot, empty_s + nslot * 8u, dfull_s);
+                    if (lane == 0 && (tc::smem_arrive_count(ps_s + kCnt + nslot * 4u) & 1u) == 1u)
+                        issue_layer0(tmem_lane, layers, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
                     break;
                 }
-                uint32_t w_off, n_next, k_next;   // the layer that consumes what this step writes
                 if (!last) {
                     tc::relu32_to_tmem(t_d, t_h);
                     tc::relu32_to_tmem(t_d + 32, t_h + 16);
-                    const bool next_last = l + 1 == (int)(in_color ? nc.nh_color : nc.nh_sigma) + 1;
-                    w_off = (in_color ? wm.c0 : wm.s0) + 4096u + (uint32_t)l * 8192u;   // [32->64] is 4 KB, [64->64] 8 KB
-                    n_next = next_last ? 16u : 64u;
-                    k_next = 64u;
                 } else {   // end of the sigma net
                     uint4 sh_lo, sh_hi;
                     sh_to_half(dx, dy, dz, sh_lo, sh_hi);
                     sg = tc::sigma_and_color_input(t_d, t_h, nc.density_scale, sh_lo, sh_hi);
-                    w_off = wm.c0; n_next = 64u; k_next = 32u;
                 }
                 tc::tmem_st_wait();
                 tc::fence_before_sync();
                 __syncwarp();
-                if (lane == 0 && (tc::smem_arrive_count(cnt_s) & 3u) == 3u) {   // the operand is complete: issue the next layer
+                if (lane == 0) {   // this warp's rows of the operand are complete: run the next layer for them, nobody else is involved
                     tc::fence_after_sync();
-                    tc::issue_layer_ts(base + tc::kColD, base + tc::kColH, w_saddr + w_off, n_next, k_next);
-                    tc::mma_commit(dfull_s);
+                    issue_layer(layers[step + 1], base + tc::kColD, base + tc::kColH, q);   // consumes what this step wrote
+                    tc::mma_commit(ps_s + kDfull);
                 }
                 __syncwarp();
                 NGP_PROF(4)
             }
 #else
             {   // no MLPs: consume layer 0's (empty) commit, hand D back
-                tc::mbar_wait(dfull_s, par);
+                tc::mbar_wait(ps_s + kDfull, par);
                 par ^= 1u;
                 tc::fence_after_sync();
                 sg = 1.0f + (float)(lane & 1); cr = cg = cbl = 0.5f;
                 tc::fence_before_sync();
                 __syncwarp();
                 const uint32_t nslot = (P + 1u) & 1u;
-                if (lane == 0 && (tc::smem_arrive_count(cnt_e_s + nslot * 4u) & 7u) == 7u)
-                    issue_layer0(tmem_lane, w_saddr, nslot, empty_s + nslot * 8u, dfull_s);
+                if (lane == 0 && (tc::smem_arrive_count(ps_s + kCnt + nslot * 4u) & 1u) == 1u)
+                    issue_layer0(tmem_lane, layers, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
             }
 #endif
             const float dt = sample_dt(ra.mc, sc.x);
-            if (K == 1) {
-                if (active && composite_sample(a, sg, cr, cg, cbl, dt, sc.y)) {   // raymarching.cu:866-894
-                    dead = true;
-                    death = chunk;
-                    samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
-                }
-                if (++in_chunk == s) { in_chunk = 0; chunk++; }
-            } else {
+            if (K > 1) {
                 scr[0] = make_float4(sg, cr, cg, cbl);
                 scr[1] = make_float4(dt, sc.y, 0.f, 0.f);
                 __syncwarp();
-                if (leader && has_ray && !dead) {   // composite this pass's <= K samples of the ray in order
-                    const uint32_t cnt = min(K, ne - min(ne, i0));
-                    for (uint32_t k = 0; k < cnt; k++) {
-                        const float4 o = scr[2 * k], dd = scr[2 * k + 1];
-                        if (composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y)) {
-                            dead = true;
-                            death = chunk;
-                            samples += min(ne, (chunk + 1) * s);
-                            break;
-                        }
-                        if (++in_chunk == s) { in_chunk = 0; chunk++; }
-                    }
-                }
-                dead = __shfl_sync(0xffffffffu, dead, lead_lane);
             }
-            {   // tell the gather team which rows it may skip from now on (a hint: a stale or foreign word only costs work)
+            if (leader && has_ray && !dead && i0 < ne) {   // composite this pass's <= K samples of the ray in order (raymarching.cu:866-894)
+                const float4 s0 = rs[0], s1 = rs[1], s2 = rs[2];
+                RayAcc a = {s0.x, s0.y, s0.z, s1.x, s1.y, s1.z};
+                uint32_t samples = __float_as_uint(s0.w), death = __float_as_uint(s1.w), chunk = __float_as_uint(s2.x), in_chunk = __float_as_uint(s2.y);
+                const uint32_t cnt = min(K, ne - i0);
+                for (uint32_t k = 0; k < cnt; k++) {
+                    float4 o = make_float4(sg, cr, cg, cbl), dd = make_float4(dt, sc.y, 0.f, 0.f);
+                    if (K > 1) { o = scr[2 * k]; dd = scr[2 * k + 1]; }
+                    if (composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y)) {
+                        dead = true;
+                        death = chunk;
+                        samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
+                        break;
+                    }
+                    if (++in_chunk == s) { in_chunk = 0; chunk++; }
+                }
+                rs[0] = make_float4(a.t, a.ws, a.d, __uint_as_float(samples));
+                rs[1] = make_float4(a.r, a.g, a.b, __uint_as_float(death));
+                rs[2] = make_float4(__uint_as_float(chunk), __uint_as_float(in_chunk), 0.f, 0.f);
+            }
+            if (K > 1) dead = __shfl_sync(0xffffffffu, dead, lead_lane);
+            {   // tell the gather warp which rows it may skip from now on (a hint: a stale or foreign word only costs work)
                 const uint32_t dm = __ballot_sync(0xffffffffu, dead);
-                if (lane == 0) *reinterpret_cast<volatile unsigned long long *>(&ss.dead[q]) = ((unsigned long long)(gtile + 1u) << 32) | dm;
+                if (lane == 0) *reinterpret_cast<volatile unsigned long long *>(&ps.dead) = ((unsigned long long)(tile + 1u) << 32) | dm;
             }
             NGP_PROF(4)
         }
         // ---- end of the epoch for these rays: who survives (raymarching.cu:896-911), tentative state, next live list
         bool survives = false;
         if (has_ray && leader) {
+            const float4 s0 = rs[0], s1 = rs[1];
+            RayAcc a = {s0.x, s0.y, s0.z, s1.x, s1.y, s1.z};
+            uint32_t samples = __float_as_uint(s0.w), death = __float_as_uint(s1.w);
             if (!dead) {
                 samples += ne;
                 if (ne < ES) { dead = true; death = ne / s; }   // the chunk that came up short: delta == 0 sentinel (:860-863)
                 else survives = true;
             }
             if (dead) atomicAdd(s_hist + death, 1u);
-            else if (a.ws > 0.9f && __ldcg(&ec->opaque) == 0u) atomicExch(&ec->opaque, 1u);   // rare: at most a few writers per epoch
+            else if (__float_as_uint(a.ws) > __ldcg(&ec->opaque)) atomicMax(&ec->opaque, __float_as_uint(a.ws));   // how far has the most opaque ray got
             float4 *so = state_out + 2 * (size_t)index;
             __stcg(so, make_float4(a.t, a.ws, a.d, __uint_as_float(seq)));
             __stcg(so + 1, make_float4(a.r, a.g, a.b, __uint_as_float(samples)));
@@ -902,6 +925,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
             if (survives) __stcg(alive_out + b0 + __popc(ballot & lt_mask), index);
         }
         NGP_PROF(0)
+      }
     }
 #undef NGP_PROF
 }
@@ -920,9 +944,10 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch], s_mval[kMaxEpoch];
-    __shared__ StreamSync s_sync[kStreams];
+    __shared__ PairSync s_sync[kGatherWarps];   // pair = (stream, lane quadrant) = gather warp index = epilogue warp index - 16
     __shared__ uint32_t s_tmem;
-    // dynamic shared memory: [tcgen05 weights][compositing scratch, 1 KB per epilogue warp][coarse occupancy, optional]
+    __shared__ LayerDesc s_layers[kMaxLayers];
+    // dynamic shared memory: [tcgen05 weights][compositing scratch + ray state, 2.5 KB per epilogue warp][coarse occupancy, optional]
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
     float4 *s_scratch = reinterpret_cast<float4 *>(s_w + nc.wtc_bytes / 16);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -930,7 +955,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     const int stream = (warp & (kGatherWarps - 1)) >> 2, q = warp & 3;
     // coarse occupancy: a shared-memory copy (NGP_COARSE_SMEM) or the global array itself (4 KB, stays in L1)
     const bool coarse_in_smem = NGP_COARSE_SMEM != 0 && ra.coarse != nullptr;
-    uint32_t *s_coarse = coarse_in_smem ? reinterpret_cast<uint32_t *>(s_scratch + (size_t)kEpiWarps * 64) : const_cast<uint32_t *>(ra.coarse);
+    uint32_t *s_coarse = coarse_in_smem ? reinterpret_cast<uint32_t *>(s_scratch + (size_t)kEpiWarps * kScratchPerWarp) : const_cast<uint32_t *>(ra.coarse);
     const uint32_t N = ra.N;
     const uint32_t lt_mask = (1u << lane) - 1u;
     long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -940,19 +965,19 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     if (coarse_in_smem)
         for (uint32_t i = tid; i < ra.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(ra.coarse + i);
     if (tid < kMaxEpoch) s_hist[tid] = 0;
+    layer_table_init(s_layers, nc, tc::smem_u32(s_w), tid);
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(&s_tmem), kRenderTmemCols);
     if (tid == 0) {
-        for (int g = 0; g < kStreams; g++) stream_sync_init(s_sync[g]);
+        for (int g = 0; g < kGatherWarps; g++) pair_sync_init(s_sync[g]);
         tc::mbar_init_fence();
-        for (int g = 0; g < kStreams; g++) stream_sync_prearm(s_sync[g]);
+        for (int g = 0; g < kGatherWarps; g++) pair_sync_prearm(s_sync[g]);
     }
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(&s_tmem);
     const uint32_t tmem_lane = tmem_base + (uint32_t)stream * kStreamCols + ((uint32_t)(q * 32) << 16);
-    const uint32_t w_saddr = tc::smem_u32(s_w);
-    StreamSync &ss = s_sync[stream];
+    PairSync &ss = s_sync[warp & (kGatherWarps - 1)];
     uint32_t passes = 0, tiles = 0, par = 0;   // the stream's pipeline position (see gather_role / epilogue_role): lives across epochs
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
@@ -969,7 +994,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     }
     grid.sync();
 
-    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = ra.rate0, E = 1, replays = 0, t_deaths = 0;
+    uint32_t n_alive = N, step = 0, iter = 0, attempt = 0, in = 0, last_rate = ra.rate0, E = 1, replays = 0, t_deaths = 0, horizon = 0xffffffffu;
     bool replay = false;
     while (step < ra.max_steps && n_alive > 0) {
         const uint32_t s = clamp_n_step(N, n_alive);                         // renderer.py:357
@@ -985,6 +1010,11 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             }
             if (ra.max_epoch && E > ra.max_epoch) E = ra.max_epoch;
             if (iter == 0 && ra.e0_cap && E > ra.e0_cap) E = ra.e0_cap;
+            if (step < ra.early_steps && E * s > ra.early_cap) E = ra.early_cap / s > 1u ? ra.early_cap / s : 1u;
+            if (E * s > horizon) {   // do not run into the first transmittance deaths blind: beyond 32 samples an epoch needs the horizon's consent
+                const uint32_t lim = horizon > 32u ? horizon : 32u;
+                if (E * s > lim) E = lim / s > 1u ? lim / s : 1u;
+            }
         }
         {
             const uint32_t left = (ra.max_steps - step + s - 1) / s;         // iterations the `while step < max_steps` loop still allows
@@ -1039,16 +1069,16 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             E = ok_iters;
             ES = E * s;
         }
-        if (tid < 4 * kStreams) s_sync[tid >> 2].dead[tid & 3] = 0ull;   // the skip hints are keyed by tile number: none survives an epoch
+        if (tid < kGatherWarps) s_sync[tid].dead = 0ull;   // the skip hints are keyed by tile number: none survives an epoch
         __syncthreads();   // s_val is rewritten below
         if (kProf) pc[2] += clock64() - g0;
         if (is_gather) {
             set_max_regs_inc<NGP_GATHER_REGS>();
-            gather_role<kProf>(nc, ra, ss, tmem_lane, w_saddr, lane, q, &ec->ticket, alive_in, n_alive, ES, tg, passes, tiles, pc);
+            gather_role<kProf>(nc, ra, ss, tmem_lane, s_layers, lane, q, &ec->ticket, alive_in, n_alive, ES, tg, passes, tiles, pc);
             set_max_regs_dec<NGP_GATHER_REGS ? 64 : 0>();
         } else {
             set_max_regs_dec<NGP_EPI_REGS>();
-            epilogue_role<kProf>(nc, ra, ss, tmem_lane, w_saddr, s_scratch + (size_t)(warp - kGatherWarps) * 64, lane, q, lt_mask, alive_in,
+            epilogue_role<kProf>(nc, ra, ss, tmem_lane, s_layers, s_scratch + (size_t)(warp - kGatherWarps) * kScratchPerWarp, lane, q, lt_mask, alive_in,
                                  alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, passes, tiles, par, pc);
             set_max_regs_inc<NGP_EPI_REGS ? 64 : 0>();
         }
@@ -1091,7 +1121,16 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         // the rays that miss the box all die in iteration 0: that burst says nothing about the rate of the iterations after it
         last_rate = (iter == ran && ran == 1u) ? ra.rate0 : last;
         // be conservative as soon as rays die by transmittance -- or are about to (a ray has lost 90 % of its light)
-        t_deaths = (any_t || __ldcg(&ec->opaque) != 0u) ? 1u : 0u;
+        const float ws_max = __uint_as_float(__ldcg(&ec->opaque));
+        t_deaths = (any_t || ws_max > 0.9f) ? 1u : 0u;
+        // Transmittance horizon: the most opaque ray has lost ws_max of its light in `step` samples; at that rate it reaches T = 1e-4
+        // after step * ln(1e-4) / ln(1 - ws_max) samples.  Epochs stay within a fraction of what is left (a heuristic: it costs a replay,
+        // never correctness, when the density ahead is higher than the density behind).
+        if (ws_max > 1e-6f && ws_max < 1.0f) {
+            const float total = (float)step * __fdividef(-9.2103404f, __logf(1.0f - ws_max));
+            const float left = total - (float)step;
+            horizon = left < 32.0f ? 16u : (left > 4.0e6f ? 0xffffffffu : (uint32_t)(left * (1.0f / ra.horizon_div)));
+        } else horizon = ws_max >= 1.0f ? 16u : 0xffffffffu;
         n_alive = na;
         in ^= 1;
     }
@@ -1182,7 +1221,7 @@ struct ngp_ctx {
 };
 
 static size_t fwd_smem_bytes(const NetConst &nc) { return (size_t)nc.wpack_count * 8 + kTile * (kEncStride + kShStride) * 2; }
-static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kEpiWarps * 64 * sizeof(float4) + NGP_EXTRA_SMEM; }
+static size_t render_smem_bytes(const NetConst &nc) { return (size_t)nc.wtc_bytes + (size_t)kEpiWarps * kScratchPerWarp * sizeof(float4) + NGP_EXTRA_SMEM; }
 
 // Frees a set of device buffers and nulls the pointers (a failed re-allocation must not leave anything dangling).
 template <class... T>
@@ -1273,7 +1312,7 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
         if (int rc = after_launch("pack_network_tc")) return rc;
         nc.wtc = c->wtc;
         nc.wtc_bytes = wm.total;
-        c->fwd_tc_smem = wm.total + 16;
+        c->fwd_tc_smem = wm.total + 64;
         NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
         NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
     }
@@ -1446,6 +1485,8 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     }
     ra.e0_cap = op.e0_cap;
     ra.rate0 = N / (op.rate0_div ? op.rate0_div : 1u) + 1u;
+    ra.early_cap = op.early_cap < 1u ? 1u : op.early_cap; ra.early_steps = op.early_steps;
+    ra.horizon_div = (float)(op.horizon_div < 1u ? 1u : op.horizon_div);
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
     ra.coarse = nullptr; ra.coarse_words = 0;
@@ -1535,7 +1576,8 @@ int ngp_ctx_set_option(ngp_ctx *c, const char *name, uint64_t value) {
     const struct { const char *name; uint32_t RenderOptions::*field; } table[] = {
         {"rows_per_ray", &RenderOptions::rows_per_ray}, {"max_epoch", &RenderOptions::max_epoch}, {"kshift", &RenderOptions::kshift},
         {"t_div", &RenderOptions::t_div}, {"t_cap", &RenderOptions::t_cap}, {"e0_cap", &RenderOptions::e0_cap},
-        {"rate0_div", &RenderOptions::rate0_div}, {"no_coarse", &RenderOptions::no_coarse},
+        {"rate0_div", &RenderOptions::rate0_div}, {"no_coarse", &RenderOptions::no_coarse}, {"early_cap", &RenderOptions::early_cap},
+        {"early_steps", &RenderOptions::early_steps}, {"horizon_div", &RenderOptions::horizon_div},
     };
     for (const auto &t : table)
         if (strcmp(t.name, name) == 0) {
@@ -1543,7 +1585,7 @@ int ngp_ctx_set_option(ngp_ctx *c, const char *name, uint64_t value) {
             c->opt.*(t.field) = (uint32_t)value;
             return 0;
         }
-    NGP_REQUIRE(false, "ctx_set_option: unknown option '%s' (rows_per_ray, max_epoch, kshift, t_div, t_cap, e0_cap, rate0_div, no_coarse)", name);
+    NGP_REQUIRE(false, "ctx_set_option: unknown option '%s' (rows_per_ray, max_epoch, kshift, t_div, t_cap, e0_cap, rate0_div, no_coarse, early_cap, early_steps, horizon_div)", name);
     return 1;
 }
 

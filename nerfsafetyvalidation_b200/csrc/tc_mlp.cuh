@@ -143,6 +143,19 @@ __device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uin
         "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// The same with an output-lane mask: D lanes whose bit is set in {m0..m3} (lane 32 j + i = bit i of m_j) are NOT written.  One warp
+// can thereby run the MMA for ITS 32 rows only -- the other 96 rows of A are read but their results are discarded -- which makes
+// the four lane quadrants of a tile independent of each other: no rendezvous of four warps per layer.
+__device__ __forceinline__ void mma_f16_ts_masked(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate,
+                                                  uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, {%5, %6, %7, %8}, p;\n\t"
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(m0), "r"(m1), "r"(m2), "r"(m3)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_st2(uint32_t taddr, uint32_t a, uint32_t b) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(a), "r"(b) : "memory");
@@ -193,6 +206,15 @@ __device__ __forceinline__ void issue_layer_ts(uint32_t tmem_d, uint32_t tmem_a,
         mma_f16_ts(tmem_d, tmem_a + k * 8, bd, idesc, k > 0 ? 1u : 0u);
     }
 }
+// ... for the 32 rows of lane quadrant q only (see mma_f16_ts_masked)
+__device__ __forceinline__ void issue_layer_ts_quadrant(uint32_t tmem_d, uint32_t tmem_a, uint32_t w_saddr, uint32_t N, uint32_t K, int q) {
+    const uint32_t idesc = instr_desc(N);
+    const uint32_t m0 = q == 0 ? 0u : 0xffffffffu, m1 = q == 1 ? 0u : 0xffffffffu, m2 = q == 2 ? 0u : 0xffffffffu, m3 = q == 3 ? 0u : 0xffffffffu;
+    for (uint32_t k = 0; k < K / 16; k++) {
+        const uint64_t bd = smem_desc(w_saddr + k * 2 * (N * 16), N * 16, 128);
+        mma_f16_ts_masked(tmem_d, tmem_a + k * 8, bd, idesc, k > 0 ? 1u : 0u, m0, m1, m2, m3);
+    }
+}
 // CTA-scope acq_rel arrival counter in shared memory: returns the value before the increment
 __device__ __forceinline__ uint32_t smem_arrive_count(uint32_t saddr) {
     uint32_t old;
@@ -233,7 +255,7 @@ __device__ __forceinline__ void pack_weight_chunks(const __half *__restrict__ W,
     }
 }
 
-// ---- one warpgroup, one 128-row tile, activations in tensor memory (the stand-alone network kernels)
+// ---- one warp, its 32 rows of a 128-row tile, activations in tensor memory (the stand-alone network kernels)
 // TMEM columns of a tile, relative to its base: accumulators D, hidden activations H (64 halves = 32 columns), and the first
 // layer's operand E (the 32-half hash-grid encoding = 16 columns).
 constexpr uint32_t kColD = 0, kColH = 64, kColE = 96;
@@ -241,27 +263,27 @@ constexpr uint32_t kTmemColsTs = 128;   // power of two >= 112
 
 struct Tile {
     uint32_t w_saddr;     // packed weights (shared-space address of the blob)
-    uint32_t mbar_saddr;  // one mbarrier (count 1) owned by this warpgroup
-    uint32_t tmem;        // TMEM address of the tile's first column, lane field = this WARP's first lane
-    uint32_t bar_id;      // named barrier of this warpgroup (1..15)
+    uint32_t mbar_saddr;  // one mbarrier (count 1) owned by this WARP
+    uint32_t tmem;        // TMEM address of the tile's first column, lane field = this warp's first lane
+    int q;                // this warp's lane quadrant (warp index % 4)
     uint32_t parity;      // phase of the mbarrier
 };
 
-// One layer: D[128 x N] = A[128 x K] (TMEM columns a_col ..) * W[N x K]^T (smem).  All 128 threads call it after their tcgen05.st of
-// the A rows; on return the accumulators are readable with tcgen05.ld.
-__device__ __forceinline__ void layer_ts(Tile &t, int row, uint32_t a_col, uint32_t w_off, uint32_t N, uint32_t K) {
-    tmem_st_wait();          // this thread's A-row stores have landed in tensor memory
-    fence_before_sync();     // ... and are ordered, with its tcgen05.ld of the previous accumulators, before the barrier
-    group_sync(t.bar_id);
-    if (row == 0) {
+// One layer for this warp's 32 rows: D[32 x N] = A[32 x K] (TMEM columns a_col ..) * W[N x K]^T (smem), as an M = 128 MMA whose other
+// three lane quadrants are masked out.  All 32 lanes call it after their tcgen05.st of the A rows; on return the accumulators are
+// readable with tcgen05.ld.  No other warp is involved.
+__device__ __forceinline__ void layer_ts(Tile &t, int lane, uint32_t a_col, uint32_t w_off, uint32_t N, uint32_t K) {
+    tmem_st_wait();          // this warp's A-row stores have landed in tensor memory
+    fence_before_sync();     // ... and are ordered, with its tcgen05.ld of the previous accumulators, before the hand-over to lane 0
+    __syncwarp();
+    if (lane == 0) {
         fence_after_sync();
-        const uint32_t base = t.tmem & 0x0000FFFFu;   // lane 0
-        issue_layer_ts(base + kColD, base + a_col, t.w_saddr + w_off, N, K);
+        const uint32_t base = t.tmem & 0x0000FFFFu;   // lane 0 of the tile
+        issue_layer_ts_quadrant(base + kColD, base + a_col, t.w_saddr + w_off, N, K, t.q);
         mma_commit(t.mbar_saddr);
-        mbar_wait(t.mbar_saddr, t.parity);   // one poller per warpgroup; the other 127 threads sleep in the hardware barrier below
     }
+    mbar_wait(t.mbar_saddr, t.parity);
     t.parity ^= 1u;
-    group_sync(t.bar_id);
     fence_after_sync();
 }
 __device__ __forceinline__ void relu_row_ts(const Tile &t) {
@@ -293,39 +315,39 @@ __device__ __forceinline__ void rgb_from_acc(uint32_t t_d, float &r, float &g, f
 // Both MLPs for the 128 rows of one warpgroup.  Precondition: every thread stored its row's hash-grid encoding (32 halves) to the
 // 16 TMEM columns at kColE.  sh_lo / sh_hi: the row's 16 SH halves.  Returns this row's sigma and rgb with the dtype flow of the
 // reference under autocast (network_ff.py:56-72): sigma = exp(float(half h0)) * density_scale, rgb = half(sigmoid(float(half h))).
-__device__ __forceinline__ void mlp_tile128(Tile &t, int row, uint32_t nh_sigma, uint32_t nh_color, float density_scale, const uint4 &sh_lo,
+__device__ __forceinline__ void mlp_tile128(Tile &t, int lane, uint32_t nh_sigma, uint32_t nh_color, float density_scale, const uint4 &sh_lo,
                                             const uint4 &sh_hi, float &sigma, float &r, float &g, float &b) {
     const WeightMap wm = weight_map(nh_sigma, nh_color);
-    layer_ts(t, row, kColE, wm.s0, 64, 32);
+    layer_ts(t, lane, kColE, wm.s0, 64, 32);
     relu_row_ts(t);
     for (uint32_t k = 0; k < nh_sigma; k++) {
-        layer_ts(t, row, kColH, wm.sh + k * 8 * 64 * 16, 64, 64);
+        layer_ts(t, lane, kColH, wm.sh + k * 8 * 64 * 16, 64, 64);
         relu_row_ts(t);
     }
-    layer_ts(t, row, kColH, wm.sl, 16, 64);
+    layer_ts(t, lane, kColH, wm.sl, 16, 64);
     sigma = sigma_and_color_input(t.tmem + kColD, t.tmem + kColH, density_scale, sh_lo, sh_hi);
-    layer_ts(t, row, kColH, wm.c0, 64, 32);
+    layer_ts(t, lane, kColH, wm.c0, 64, 32);
     relu_row_ts(t);
     for (uint32_t k = 0; k < nh_color; k++) {
-        layer_ts(t, row, kColH, wm.ch + k * 8 * 64 * 16, 64, 64);
+        layer_ts(t, lane, kColH, wm.ch + k * 8 * 64 * 16, 64, 64);
         relu_row_ts(t);
     }
-    layer_ts(t, row, kColH, wm.cl, 16, 64);
+    layer_ts(t, lane, kColH, wm.cl, 16, 64);
     rgb_from_acc(t.tmem + kColD, r, g, b);
 }
 
 // The density net alone for the 128 rows of one warpgroup (NeRFNetwork.density, network_ff.py:76-89).  Same precondition as
 // mlp_tile128.  h[16]: the row's sigma-net outputs rounded to half as the reference's FFMLP stores them (h[0] = log-density,
 // h[1..15] = geo_feat).
-__device__ __forceinline__ void sigma_tile128(Tile &t, int row, uint32_t nh_sigma, float (&h)[16]) {
+__device__ __forceinline__ void sigma_tile128(Tile &t, int lane, uint32_t nh_sigma, float (&h)[16]) {
     const WeightMap wm = weight_map(nh_sigma, 0);
-    layer_ts(t, row, kColE, wm.s0, 64, 32);
+    layer_ts(t, lane, kColE, wm.s0, 64, 32);
     relu_row_ts(t);
     for (uint32_t k = 0; k < nh_sigma; k++) {
-        layer_ts(t, row, kColH, wm.sh + k * 8 * 64 * 16, 64, 64);
+        layer_ts(t, lane, kColH, wm.sh + k * 8 * 64 * 16, 64, 64);
         relu_row_ts(t);
     }
-    layer_ts(t, row, kColH, wm.sl, 16, 64);
+    layer_ts(t, lane, kColH, wm.sl, 16, 64);
     tmem_ld16(t.tmem + kColD, h);
 #pragma unroll
     for (int i = 0; i < 16; i++) h[i] = __half2float(__float2half_rn(h[i]));

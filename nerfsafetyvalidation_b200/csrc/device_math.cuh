@@ -273,6 +273,7 @@ __device__ __forceinline__ uint32_t grid_row_fast(const LevelConst &lc, uint32_t
 // The 8 table rows of the cell whose low corner is (g0, g1, g2); corner k = (k & 1, (k >> 1) & 1, (k >> 2) & 1), the order
 // the reference accumulates in (gridencoder.cu:146-171).  lc.mode is uniform per level, so the branch never diverges, and the
 // two common modes share the per-axis terms between corners instead of recomputing the hash / dense index 8 times.
+template <bool kGeneral = true>
 __device__ __forceinline__ void cell_rows(const LevelConst &lc, uint32_t g0, uint32_t g1, uint32_t g2, uint32_t (&row)[8]) {
     if (lc.mode == 1) {            // hashed level, power-of-two table: (x ^ y*P1 ^ z*P2) & (T - 1); (g+1)*P = g*P + P mod 2^32
         const uint32_t m = lc.size - 1u;
@@ -286,9 +287,13 @@ __device__ __forceinline__ void cell_rows(const LevelConst &lc, uint32_t g0, uin
         const uint32_t b = g0 + (g1 + g2 * s1) * s1;
         row[0] = b; row[1] = b + 1u; row[2] = b + s1; row[3] = b + s1 + 1u;
         row[4] = b + s2; row[5] = b + s2 + 1u; row[6] = b + s2 + s1; row[7] = b + s2 + s1 + 1u;
-    } else {                       // non-power-of-two hash table or wrapped dense level: the general form
+    } else if (kGeneral) {         // non-power-of-two hash table or wrapped dense level: the general form (integer divisions; the
+                                   // persistent renderer is built without it and refuses such tables, which no NGP configuration produces)
 #pragma unroll
         for (int k = 0; k < 8; k++) row[k] = grid_row_fast(lc, g0 + (k & 1), g1 + ((k >> 1) & 1), g2 + ((k >> 2) & 1));
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; k++) row[k] = 0u;
     }
 }
 

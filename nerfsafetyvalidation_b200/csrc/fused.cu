@@ -41,6 +41,12 @@ struct NetConst {
     float bound, two_bound, density_scale;
     LevelConst lv[kMaxLevels];
     const __half2 *lvbase[kMaxLevels];   // table + lv[l].offset: one 64-bit base per level, 32-bit row offsets in the gather
+    // The renderer's MMAs, layer by layer in evaluation order (sigma net, then colour net), as kernel PARAMETERS: the issuing thread reads
+    // them from the constant bank straight into uniform registers.  ldesc_b = shared-memory descriptor of the layer's first weight
+    // K-chunk with the address field relative to the weight blob (the kernel adds its blob address); chunk k is + k * bstep.
+    uint64_t ldesc_b[10];
+    uint32_t ldesc_i[10];          // instruction descriptor (N = 64 | 16)
+    uint32_t ldesc_nk_bstep[10];   // (K / 16) << 16 | bstep
 };
 
 // ---------------------------------------------------------------------------------------------- device pieces
@@ -68,7 +74,7 @@ __device__ __forceinline__ bool encode_unit(const NetConst &nc, float x, float y
 #endif
 constexpr int kRenderLevelsPerTrip = NGP_LEVELS_PER_TRIP;   // the renderer: 20 warps per SM at 96 registers (A/B in DESIGN.md section 8)
 
-template <int LPT>
+template <int LPT, bool kGeneral = true>
 __device__ __forceinline__ void encode_trip(const NetConst &nc, float u0, float u1, float u2, int trip, uint32_t (&packed)[LPT]) {
     float f[LPT][3];
     __half2 v[LPT][8];
@@ -81,7 +87,7 @@ __device__ __forceinline__ void encode_trip(const NetConst &nc, float u0, float 
         f[j][0] = __fsub_rn(p0, (float)g0); f[j][1] = __fsub_rn(p1, (float)g1); f[j][2] = __fsub_rn(p2, (float)g2);
         const __half2 *tl = nc.lvbase[trip * LPT + j];
         uint32_t row[8];
-        cell_rows(lc, g0, g1, g2, row);
+        cell_rows<kGeneral>(lc, g0, g1, g2, row);
 #pragma unroll
         for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
     }
@@ -128,7 +134,7 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
 // 16-level hash-grid encoding of one point -> the 16 TMEM columns at taddr (this thread's lane).  tcgen05.st is warp-collective:
 // every lane calls this; lanes with !active store zeros without gathering (the reference's encoding of a point outside the unit
 // cube is zero as well, gridencoder.cu:99-123).
-template <int LPT>
+template <int LPT, bool kGeneral = true>
 __device__ __forceinline__ void encode_point_tmem(const NetConst &nc, float x, float y, float z, bool active, uint32_t taddr) {
     static_assert(LPT == 4 || LPT == 2, "a trip stores 4 or 2 columns");
     float u0 = 0.f, u1 = 0.f, u2 = 0.f;
@@ -139,7 +145,7 @@ __device__ __forceinline__ void encode_point_tmem(const NetConst &nc, float x, f
         uint32_t packed[LPT];
 #pragma unroll
         for (int j = 0; j < LPT; j++) packed[j] = 0u;
-        if (inside) encode_trip<LPT>(nc, u0, u1, u2, trip, packed);
+        if (inside) encode_trip<LPT, kGeneral>(nc, u0, u1, u2, trip, packed);
         __syncwarp();
         if (LPT == 4) tc::tmem_st4(taddr + (uint32_t)trip * 4u, make_uint4(packed[0], packed[1], packed[2], packed[LPT - 1]));
         else tc::tmem_st2(taddr + (uint32_t)trip * 2u, packed[0], packed[1]);
@@ -437,7 +443,7 @@ constexpr int kMaxEpoch = 128;                 // reference iterations per epoch
 #define NGP_MAX_SAMPLES_PER_EPOCH 128
 #endif
 constexpr int kMaxSamplesPerEpoch = NGP_MAX_SAMPLES_PER_EPOCH;      // E * s cap: bounds the longest tile of an epoch
-constexpr int kScratchPerWarp = 32 * (2 + 3);   // float4 per epilogue warp: compositing scratch (2 per lane) + ray state (3 per lane)
+constexpr int kScratchPerWarp = 32 * (2 + 3 + 2);   // float4 per epilogue warp: compositing scratch (2 per lane) + ray state (3) + SH row (2)
 constexpr uint32_t kTilesPerTicket = 1;      // EVALUATE: consecutive 32-row warp tiles (adjacent rays: shared hash-grid cells) per claimed ticket
 constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
 
@@ -635,47 +641,86 @@ __device__ __forceinline__ uint32_t ticket_consume(PairSync &ps, uint32_t T, int
     return t;
 }
 
-// The MMAs of every layer, prepared once per launch in shared memory: the issuing lane only loads descriptors and fires.
 constexpr int kMaxLayers = 10;   // 2 nets x (first + <= 3 hidden + last)
-struct __align__(16) LayerDesc {
-    uint64_t bdesc[4];   // shared-memory descriptors of the weight K-chunks (16 columns of K each)
-    uint32_t idesc;      // instruction descriptor (N = 64 | 16)
-    uint32_t nk;         // K / 16
-    uint32_t pad[2];
-};
-__device__ __forceinline__ void layer_table_init(LayerDesc *tab, const NetConst &nc, uint32_t w_saddr, int tid) {   // threads 0 .. n_all - 1
+static void layer_table_init(NetConst &nc) {   // host, ngp_ctx_set_network
     const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
     const int n_sig = 2 + (int)nc.nh_sigma, n_all = n_sig + 2 + (int)nc.nh_color;
-    if (tid >= n_all) return;
-    const bool in_color = tid >= n_sig;
-    const int l = in_color ? tid - n_sig : tid;
-    const bool first = l == 0, last = l == (int)(in_color ? nc.nh_color : nc.nh_sigma) + 1;
-    const uint32_t w_off = (in_color ? wm.c0 : wm.s0) + (first ? 0u : 4096u + (uint32_t)(l - 1) * 8192u);   // [32->64] is 4 KB, [64->64] 8 KB
-    const uint32_t N = last ? 16u : 64u, K = first ? 32u : 64u;
-    LayerDesc d;
-    for (uint32_t k = 0; k < 4; k++) d.bdesc[k] = tc::smem_desc(w_saddr + w_off + k * 2 * (N * 16), N * 16, 128);
-    d.idesc = tc::instr_desc(N); d.nk = K / 16; d.pad[0] = d.pad[1] = 0;
-    tab[tid] = d;
-}
-// One layer for lane quadrant q: D = A (TMEM columns from tmem_a) x W^T.  One thread.
-__device__ __forceinline__ void issue_layer(const LayerDesc &ld, uint32_t tmem_d, uint32_t tmem_a, int q) {
-    const uint32_t m0 = q == 0 ? 0u : 0xffffffffu, m1 = q == 1 ? 0u : 0xffffffffu, m2 = q == 2 ? 0u : 0xffffffffu, m3 = q == 3 ? 0u : 0xffffffffu;
-    const uint32_t idesc = ld.idesc, nk = ld.nk;
-    tc::mma_f16_ts_masked(tmem_d, tmem_a, ld.bdesc[0], idesc, 0u, m0, m1, m2, m3);
-    tc::mma_f16_ts_masked(tmem_d, tmem_a + 8, ld.bdesc[1], idesc, 1u, m0, m1, m2, m3);
-    if (nk > 2) {
-        tc::mma_f16_ts_masked(tmem_d, tmem_a + 16, ld.bdesc[2], idesc, 1u, m0, m1, m2, m3);
-        tc::mma_f16_ts_masked(tmem_d, tmem_a + 24, ld.bdesc[3], idesc, 1u, m0, m1, m2, m3);
+    for (int i = 0; i < n_all; i++) {
+        const bool in_color = i >= n_sig;
+        const int l = in_color ? i - n_sig : i;
+        const bool first = l == 0, last = l == (int)(in_color ? nc.nh_color : nc.nh_sigma) + 1;
+        const uint32_t w_off = (in_color ? wm.c0 : wm.s0) + (first ? 0u : 4096u + (uint32_t)(l - 1) * 8192u);   // [32->64] is 4 KB, [64->64] 8 KB
+        const uint32_t N = last ? 16u : 64u, K = first ? 32u : 64u;
+        nc.ldesc_b[i] = tc::smem_desc(w_off, N * 16, 128);
+        nc.ldesc_i[i] = tc::instr_desc(N);
+        nc.ldesc_nk_bstep[i] = ((K / 16) << 16) | (2u * N);   // 2 * (N * 16) bytes per K-chunk >> 4
     }
+}
+// One layer for lane quadrant q: D = A (TMEM columns from tmem_a) x W^T.  One thread.  All K / 16 MMAs sit in ONE asm block, and every
+// operand is a warp-uniform value the compiler can prove uniform (kernel parameters, the warp index, literals), so that the uniform
+// operands are set up once per layer (a masked tcgen05.mma issued alone, from per-lane registers, costs ~19 SASS instructions).
+template <int NK>
+__device__ __forceinline__ void issue_layer_nk(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc0, uint32_t idesc, uint32_t bstep, uint32_t m0,
+                                               uint32_t m1, uint32_t m2, uint32_t m3) {
+    static_assert(NK == 2 || NK == 4, "a layer has K = 32 or K = 64");
+    if (NK == 2) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p0, p1;\n\t"
+            ".reg .b32 a1;\n\t"
+            ".reg .b64 b1, st;\n\t"
+            "setp.ne.b32 p0, 0, 0;\n\t"
+            "setp.eq.b32 p1, 0, 0;\n\t"
+            "cvt.u64.u32 st, %4;\n\t"
+            "add.u64 b1, %2, st;\n\t"
+            "add.u32 a1, %1, 8;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, {%5, %6, %7, %8}, p0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %3, {%5, %6, %7, %8}, p1;\n\t"
+            "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc0), "r"(idesc), "r"(bstep), "r"(m0), "r"(m1), "r"(m2), "r"(m3)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p0, p1;\n\t"
+            ".reg .b32 a1, a2, a3;\n\t"
+            ".reg .b64 b1, b2, b3, st;\n\t"
+            "setp.ne.b32 p0, 0, 0;\n\t"
+            "setp.eq.b32 p1, 0, 0;\n\t"
+            "cvt.u64.u32 st, %4;\n\t"
+            "add.u64 b1, %2, st; add.u64 b2, b1, st; add.u64 b3, b2, st;\n\t"
+            "add.u32 a1, %1, 8; add.u32 a2, %1, 16; add.u32 a3, %1, 24;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, {%5, %6, %7, %8}, p0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %3, {%5, %6, %7, %8}, p1;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %3, {%5, %6, %7, %8}, p1;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %3, {%5, %6, %7, %8}, p1;\n\t"
+            "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc0), "r"(idesc), "r"(bstep), "r"(m0), "r"(m1), "r"(m2), "r"(m3)
+            : "memory");
+    }
+}
+// w_desc = (shared address of the weight blob) >> 4: added to the relative descriptor (the address field holds 14 bits; 48 KB blob + base fit)
+__device__ __forceinline__ void issue_layer(const NetConst &nc, int layer, uint32_t w_desc, uint32_t tmem_d, uint32_t tmem_a, int q) {
+    const uint64_t bdesc0 = nc.ldesc_b[layer] + w_desc;
+    const uint32_t idesc = nc.ldesc_i[layer], nkb = nc.ldesc_nk_bstep[layer], bstep = nkb & 0xffffu;
+    const uint32_t m0 = q == 0 ? 0u : 0xffffffffu, m1 = q == 1 ? 0u : 0xffffffffu, m2 = q == 2 ? 0u : 0xffffffffu, m3 = q == 3 ? 0u : 0xffffffffu;
+    if ((nkb >> 16) == 4u) issue_layer_nk<4>(tmem_d, tmem_a, bdesc0, idesc, bstep, m0, m1, m2, m3);
+    else issue_layer_nk<2>(tmem_d, tmem_a, bdesc0, idesc, bstep, m0, m1, m2, m3);
+}
+
+// One arrival of this (converged) warp on a two-party counter; true in every lane iff it was the second one.
+__device__ __forceinline__ bool second_arrival(uint32_t cnt_saddr, int lane) {
+    uint32_t old = 0;
+    if (lane == 0) old = tc::smem_arrive_count(cnt_saddr);
+    return (__shfl_sync(0xffffffffu, old, 0) & 1u) == 1u;
 }
 
 // Layer 0 of a pass (A = E slot, 32 -> 64) for the pair's lane quadrant, issued by whichever of the two warps made the second arrival
 // on the slot's counter.
-__device__ __forceinline__ void issue_layer0(uint32_t tmem_lane, const LayerDesc *layers, uint32_t slot, int q, uint32_t empty_saddr, uint32_t dfull_saddr) {
+__device__ __forceinline__ void issue_layer0(const NetConst &nc, uint32_t tmem_col, uint32_t w_desc, uint32_t slot, int q, uint32_t empty_saddr, uint32_t dfull_saddr) {
     tc::fence_after_sync();
-    const uint32_t base = tmem_lane & 0x0000FFFFu;
 #ifndef NGP_ABLATE_MLP
-    issue_layer(layers[0], base + tc::kColD, base + tc::kColE + slot * 16u, q);
+    // two call sites, so that each sees a warp-uniform operand address (`slot` comes from a data-dependent pass counter)
+    if (slot) issue_layer(nc, 0, w_desc, tmem_col + tc::kColD, tmem_col + tc::kColE + 16u, q);
+    else issue_layer(nc, 0, w_desc, tmem_col + tc::kColD, tmem_col + tc::kColE, q);
 #endif
     tc::mma_commit(empty_saddr);   // the slot may be refilled ...
     tc::mma_commit(dfull_saddr);   // ... and the epilogue warp may read D once these MMAs have completed
@@ -685,7 +730,7 @@ __device__ __forceinline__ void issue_layer0(uint32_t tmem_lane, const LayerDesc
 // consecutive samples of each (lane = r * K + k = TMEM lane within the quadrant).  P / T: passes / tiles this pair has issued since the
 // kernel started (they select the E slot, the ticket slot and the barrier phases; identical in both warps of the pair).
 template <bool kProf>
-__device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs &ra, PairSync &ps, uint32_t tmem_lane, const LayerDesc *layers, int lane,
+__device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs &ra, PairSync &ps, uint32_t tmem_col, uint32_t w_desc, int lane,
                                             int q, uint32_t *ticket_ctr, const int *__restrict__ alive_in, uint32_t n_alive,
                                             uint32_t ES, const TileGeom tg, uint32_t &P, uint32_t &T, long long (&pc)[8]) {
     const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
@@ -694,6 +739,7 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
     const uint32_t tile_rows = R * tg.ESp;
     const uint32_t ps_s = tc::smem_u32(&ps);   // one base register; the fields are immediate offsets
     constexpr uint32_t kEmpty = offsetof(PairSync, empty), kCnt = offsetof(PairSync, cnt_e), kDfull = offsetof(PairSync, dfull);
+    const uint32_t tmem_lane = tmem_col + ((uint32_t)(q * 32) << 16);   // this warp's lanes of the stream's columns
     const volatile unsigned long long *dead_w = &ps.dead;
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
@@ -738,14 +784,14 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
 #else
             const bool gather_on = true;
 #endif
-            encode_point_tmem<kRenderLevelsPerTrip>(nc, sample_pos(ra.mc, ox, dx, t), sample_pos(ra.mc, oy, dy, t), sample_pos(ra.mc, oz, dz, t),
+            encode_point_tmem<kRenderLevelsPerTrip, false>(nc, sample_pos(ra.mc, ox, dx, t), sample_pos(ra.mc, oy, dy, t), sample_pos(ra.mc, oz, dz, t),
                                                     active && gather_on, tmem_lane + tc::kColE + slot * 16u);
             tc::tmem_st_wait();
             tc::fence_before_sync();
             __syncwarp();
             NGP_PROF(3)
-            if (lane == 0 && (tc::smem_arrive_count(ps_s + kCnt + slot * 4u) & 1u) == 1u)   // slot filled AND D free: issue layer 0
-                issue_layer0(tmem_lane, layers, slot, q, ps_s + kEmpty + slot * 8u, ps_s + kDfull);
+            if (second_arrival(ps_s + kCnt + slot * 4u, lane) && tc::elect_one())   // slot filled AND D free: issue layer 0
+                issue_layer0(nc, tmem_col, w_desc, slot, q, ps_s + kEmpty + slot * 8u, ps_s + kDfull);
             __syncwarp();
             NGP_PROF(5)
         }
@@ -758,7 +804,7 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
 // EPILOGUE role of one warp: every layer's activation for the pair's 32 rows, then compositing, ray state and the next live list.
 // par: phase parity of ps.dfull (one phase per layer), persistent like P and T.
 template <bool kProf>
-__device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderArgs &ra, PairSync &ps, uint32_t tmem_lane, const LayerDesc *layers,
+__device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderArgs &ra, PairSync &ps, uint32_t tmem_col, uint32_t w_desc,
                                               float4 *scratch, int lane, int q, uint32_t lt_mask,
                                               const int *__restrict__ alive_in, int *__restrict__ alive_out, const float4 *__restrict__ state_in,
                                               float4 *__restrict__ state_out, uint32_t n_alive, uint32_t s, uint32_t ES, const TileGeom tg,
@@ -772,9 +818,11 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
     const uint32_t ps_s = tc::smem_u32(&ps);   // one base register; the fields are immediate offsets
     constexpr uint32_t kEmpty = offsetof(PairSync, empty), kCnt = offsetof(PairSync, cnt_e), kDfull = offsetof(PairSync, dfull);
     const int n_sig = 2 + (int)nc.nh_sigma, n_all = n_sig + 2 + (int)nc.nh_color;
-    const uint32_t t_d = tmem_lane + tc::kColD, t_h = tmem_lane + tc::kColH, base = tmem_lane & 0x0000FFFFu;
+    const uint32_t tmem_lane = tmem_col + ((uint32_t)(q * 32) << 16);   // this warp's lanes of the stream's columns
+    const uint32_t t_d = tmem_lane + tc::kColD, t_h = tmem_lane + tc::kColH;
     float4 *scr = scratch + 2 * lane;   // this lane's 32 bytes of its warp's compositing scratch
-    float4 *rs = scratch + 64 + 3 * lane;   // ... and the 48 bytes of ray state behind it
+    float4 *rs = scratch + 64 + 3 * lane;   // ... the 48 bytes of ray state behind it
+    uint4 *shs = reinterpret_cast<uint4 *>(scratch + 160) + 2 * lane;   // ... and the 16 SH halves of this lane's ray
     long long c0 = kProf ? clock64() : 0, c1;
 #define NGP_PROF(k) if (kProf) { c1 = clock64(); pc[k] += c1 - c0; c0 = c1; }
     const uint32_t n_tickets = (n_tiles + kTilesPerTicket - 1) / kTilesPerTicket;
@@ -785,7 +833,6 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
         const bool has_ray = n < n_alive;
         uint32_t ne = 0;
         int index = 0;
-        float dx = 0.f, dy = 0.f, dz = 1.f;
         // The accumulators of a ray live in SHARED memory between passes (3 x 16 B in its leader lane's slot): only the leader lanes touch
         // them, for a few instructions per pass, and keeping them out of the register file is what keeps the layer loop free of spills.
         //   rs[0] = (t, weights_sum, depth, samples)   rs[1] = (r, g, b, death)   rs[2] = (chunk, in_chunk, -, -)
@@ -793,8 +840,8 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
             ne = min(__ldcg(ra.n_emit + n), ES);
             index = __ldcg(alive_in + n);
             const float *d = ra.rays_d + (size_t)index * 3;
-            dx = __ldg(d); dy = __ldg(d + 1); dz = __ldg(d + 2);   // the direction is constant along the ray: SH per pass from registers
-            if (leader) {
+            sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), shs[0], shs[1]);   // the direction is constant along the ray: SH once per tile,
+            if (leader) {                                                       // kept in this lane's shared-memory slot
                 const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
                 rs[0] = make_float4(r0.x, r0.y, r0.z, r1.w);
                 rs[1] = make_float4(r1.x, r1.y, r1.z, 0.f);
@@ -831,24 +878,22 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                     __syncwarp();
                     // D is free: that is one of the two arrivals layer 0 of the NEXT pass needs; if its slot is already filled, issue it here
                     const uint32_t nslot = (P + 1u) & 1u;
-                    if (lane == 0 && (tc::smem_arrive_count(ps_s + kCnt + nslot * 4u) & 1u) == 1u)
-                        issue_layer0(tmem_lane, layers, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
+                    if (second_arrival(ps_s + kCnt + nslot * 4u, lane) && tc::elect_one())
+                        issue_layer0(nc, tmem_col, w_desc, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
                     break;
                 }
                 if (!last) {
                     tc::relu32_to_tmem(t_d, t_h);
                     tc::relu32_to_tmem(t_d + 32, t_h + 16);
                 } else {   // end of the sigma net
-                    uint4 sh_lo, sh_hi;
-                    sh_to_half(dx, dy, dz, sh_lo, sh_hi);
-                    sg = tc::sigma_and_color_input(t_d, t_h, nc.density_scale, sh_lo, sh_hi);
+                    sg = tc::sigma_and_color_input(t_d, t_h, nc.density_scale, shs[0], shs[1]);
                 }
                 tc::tmem_st_wait();
                 tc::fence_before_sync();
                 __syncwarp();
-                if (lane == 0) {   // this warp's rows of the operand are complete: run the next layer for them, nobody else is involved
+                if (tc::elect_one()) {   // this warp's rows of the operand are complete: run the next layer for them, nobody else is involved
                     tc::fence_after_sync();
-                    issue_layer(layers[step + 1], base + tc::kColD, base + tc::kColH, q);   // consumes what this step wrote
+                    issue_layer(nc, step + 1, w_desc, tmem_col + tc::kColD, tmem_col + tc::kColH, q);   // consumes what this step wrote
                     tc::mma_commit(ps_s + kDfull);
                 }
                 __syncwarp();
@@ -863,8 +908,8 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                 tc::fence_before_sync();
                 __syncwarp();
                 const uint32_t nslot = (P + 1u) & 1u;
-                if (lane == 0 && (tc::smem_arrive_count(ps_s + kCnt + nslot * 4u) & 1u) == 1u)
-                    issue_layer0(tmem_lane, layers, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
+                if (second_arrival(ps_s + kCnt + nslot * 4u, lane) && tc::elect_one())
+                    issue_layer0(nc, tmem_col, w_desc, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
             }
 #endif
             const float dt = sample_dt(ra.mc, sc.x);
@@ -946,11 +991,13 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     __shared__ uint32_t s_hist[kMaxEpoch], s_val[kMaxEpoch], s_mval[kMaxEpoch];
     __shared__ PairSync s_sync[kGatherWarps];   // pair = (stream, lane quadrant) = gather warp index = epilogue warp index - 16
     __shared__ uint32_t s_tmem;
-    __shared__ LayerDesc s_layers[kMaxLayers];
-    // dynamic shared memory: [tcgen05 weights][compositing scratch + ray state, 2.5 KB per epilogue warp][coarse occupancy, optional]
+    // dynamic shared memory: [tcgen05 weights][compositing scratch + ray state + SH rows, 3.5 KB per epilogue warp][coarse occupancy, optional]
     uint4 *s_w = reinterpret_cast<uint4 *>(smem_raw);
     float4 *s_scratch = reinterpret_cast<float4 *>(s_w + nc.wtc_bytes / 16);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // the warp index through a broadcast: the compiler then knows that everything derived from it (role, stream, quadrant, TMEM columns,
+    // barrier addresses) is warp-uniform and keeps it in uniform registers -- which do not count against the 64 per thread
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const bool is_gather = warp < kGatherWarps;
     const int stream = (warp & (kGatherWarps - 1)) >> 2, q = warp & 3;
     // coarse occupancy: a shared-memory copy (NGP_COARSE_SMEM) or the global array itself (4 KB, stays in L1)
@@ -965,7 +1012,6 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     if (coarse_in_smem)
         for (uint32_t i = tid; i < ra.coarse_words; i += blockDim.x) s_coarse[i] = __ldg(ra.coarse + i);
     if (tid < kMaxEpoch) s_hist[tid] = 0;
-    layer_table_init(s_layers, nc, tc::smem_u32(s_w), tid);
     if (warp == 0) tc::tmem_alloc(tc::smem_u32(&s_tmem), kRenderTmemCols);
     if (tid == 0) {
         for (int g = 0; g < kGatherWarps; g++) pair_sync_init(s_sync[g]);
@@ -975,8 +1021,13 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
+    // All 512 columns are ours, so the allocation starts at column 0, lane 0; relying on that keeps every TMEM address a warp-uniform
+    // value the compiler can see (an address loaded from shared memory is a per-lane value to it, and every tcgen05.mma operand that is
+    // not provably uniform costs a waterfall loop at the issue site).
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t *>(&s_tmem);
-    const uint32_t tmem_lane = tmem_base + (uint32_t)stream * kStreamCols + ((uint32_t)(q * 32) << 16);
+    if (tmem_base != 0u) __trap();
+    const uint32_t tmem_col = (uint32_t)stream * kStreamCols;   // lane field 0: what the MMAs address
+    const uint32_t w_desc = (tc::smem_u32(s_w) >> 4) & 0x3FFFu;
     PairSync &ss = s_sync[warp & (kGatherWarps - 1)];
     uint32_t passes = 0, tiles = 0, par = 0;   // the stream's pipeline position (see gather_role / epilogue_role): lives across epochs
 
@@ -1074,11 +1125,11 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         if (kProf) pc[2] += clock64() - g0;
         if (is_gather) {
             set_max_regs_inc<NGP_GATHER_REGS>();
-            gather_role<kProf>(nc, ra, ss, tmem_lane, s_layers, lane, q, &ec->ticket, alive_in, n_alive, ES, tg, passes, tiles, pc);
+            gather_role<kProf>(nc, ra, ss, tmem_col, w_desc, lane, q, &ec->ticket, alive_in, n_alive, ES, tg, passes, tiles, pc);
             set_max_regs_dec<NGP_GATHER_REGS ? 64 : 0>();
         } else {
             set_max_regs_dec<NGP_EPI_REGS>();
-            epilogue_role<kProf>(nc, ra, ss, tmem_lane, s_layers, s_scratch + (size_t)(warp - kGatherWarps) * kScratchPerWarp, lane, q, lt_mask, alive_in,
+            epilogue_role<kProf>(nc, ra, ss, tmem_col, w_desc, s_scratch + (size_t)(warp - kGatherWarps) * kScratchPerWarp, lane, q, lt_mask, alive_in,
                                  alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, passes, tiles, par, pc);
             set_max_regs_inc<NGP_EPI_REGS ? 64 : 0>();
         }
@@ -1189,6 +1240,7 @@ struct ngp_ctx {
     int device = 0, sm_count = 0;
     size_t max_smem_optin = 0;
     bool has_net = false, has_scene = false;
+    bool fast_levels = false;   // every level is a plain dense grid or a power-of-two hash table (what the persistent renderer is built for)
     NetConst nc{};
     uint2 *wpack = nullptr;
     uint4 *wtc = nullptr;
@@ -1295,6 +1347,8 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
         if (!hashed) lc.mode = cube <= lc.size ? 0u : 3u;
         else lc.mode = (lc.size & (lc.size - 1)) == 0 ? 1u : 2u;
     }
+    c->fast_levels = true;
+    for (uint32_t l = 0; l < L; l++) c->fast_levels = c->fast_levels && nc.lv[l].mode <= 1u;
     const uint32_t count = 512 + nc.nh_sigma * 1024 + 256 + 512 + nc.nh_color * 1024 + 256;
     if (c->wpack) { cudaFree(c->wpack); c->wpack = nullptr; }
     NGP_CUDA(cudaMalloc(&c->wpack, sizeof(uint2) * count));
@@ -1312,6 +1366,7 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
         if (int rc = after_launch("pack_network_tc")) return rc;
         nc.wtc = c->wtc;
         nc.wtc_bytes = wm.total;
+        layer_table_init(nc);
         c->fwd_tc_smem = wm.total + 64;
         NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
         NGP_CUDA(cudaFuncSetAttribute(k_network_forward_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->fwd_tc_smem));
@@ -1457,6 +1512,8 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
                float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, void *stream) {
     NGP_REQUIRE(c != nullptr && c->has_net && c->has_scene, "render: ngp_ctx_set_network / ngp_ctx_set_scene have not been called");
     NGP_REQUIRE(max_steps >= 1, "render: max_steps must be >= 1");
+    NGP_REQUIRE(c->fast_levels, "render: a hash-grid level is neither a dense grid that fits its table nor a power-of-two hash table; "
+                                "the persistent renderer is not built for that (use the stand-alone ops: NeRFRenderer.render(fused=False))");
     if (N == 0) return 0;
     NGP_DEVPTR(rays_o); NGP_DEVPTR(rays_d); NGP_DEVPTR(image); NGP_DEVPTR(depth); NGP_DEVPTR(weights_sum);
     if (int rc = ensure_workspace(c, N)) return rc;

@@ -91,6 +91,23 @@ __device__ __forceinline__ void encode_trip(const NetConst &nc, float u0, float 
 #pragma unroll
         for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
     }
+#ifndef NGP_FP32_BLEND   // default: trilinear blend in packed fp16 (HMUL2 / HFMA2, weights and sum rounded to half like the reference's own
+                        // accumulator, gridencoder.cu:146-171) instead of fp32 FFMA2 after 16 conversions per level: -2 % frame time, and
+                        // the image's distance from the reference extensions is unchanged (1.4e-4, set by the fp32- vs fp16-accumulated MLPs)
+#pragma unroll
+    for (int j = 0; j < LPT; j++) {
+        const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
+        const __half2 wx = __floats2half2_rn(1.0f - p0, p0);
+        const __half2 hq1 = __float2half2_rn(1.0f - p1), hp1 = __float2half2_rn(p1), hq2 = __float2half2_rn(1.0f - p2), hp2 = __float2half2_rn(p2);
+        const __half2 w0 = __hmul2(wx, hq1), w1 = __hmul2(wx, hp1);
+        const __half2 w[4] = {__hmul2(w0, hq2), __hmul2(w1, hq2), __hmul2(w0, hp2), __hmul2(w1, hp2)};   // corner pairs (0,1) (2,3) (4,5) (6,7)
+        __half2 acc = __float2half2_rn(0.f);
+#pragma unroll
+        for (int k = 0; k < 8; k++) acc = __hfma2((k & 1) ? __high2half2(w[k >> 1]) : __low2half2(w[k >> 1]), v[j][k], acc);
+        packed[j] = *reinterpret_cast<const uint32_t *>(&acc);
+    }
+    return;
+#endif
 #pragma unroll
     for (int j = 0; j < LPT; j++) {
         const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
@@ -430,6 +447,17 @@ static_assert(kStreamCols == 128 && tc::kColE + 32 == kStreamCols, "a stream own
 #ifndef NGP_EPI_REGS
 #define NGP_EPI_REGS 0
 #endif
+// nanoseconds a waiter sleeps between two looks at its barrier (tc::mbar_wait): the epilogue warp waiting for a layer's MMAs, the gather
+// warp waiting for a free operand slot, either of them waiting for the next tile
+#ifndef NGP_SLEEP_LAYER
+#define NGP_SLEEP_LAYER 64
+#endif
+#ifndef NGP_SLEEP_SLOT
+#define NGP_SLEEP_SLOT 256
+#endif
+#ifndef NGP_SLEEP_TICKET
+#define NGP_SLEEP_TICKET 256
+#endif
 #ifndef NGP_EXTRA_SMEM
 #define NGP_EXTRA_SMEM 0
 #endif
@@ -623,7 +651,7 @@ __device__ __forceinline__ void pair_sync_prearm(PairSync &ps) {   // one thread
 // the epilogue warp through a two-deep ring.  All waits sleep in hardware, none polls.
 __device__ __forceinline__ uint32_t ticket_publish(PairSync &ps, uint32_t *ticket_ctr, uint32_t T, int lane) {   // gather warp
     const uint32_t ts = T & 1u;
-    tc::mbar_wait(tc::smem_u32(&ps.tempty[ts]), (T >> 1) & 1u, 0x40000000u | T);
+    tc::mbar_wait<NGP_SLEEP_TICKET>(tc::smem_u32(&ps.tempty[ts]), (T >> 1) & 1u, 0x40000000u | T);
     uint32_t t = 0;
     if (lane == 0) {
         t = atomicAdd(ticket_ctr, 1u);
@@ -634,7 +662,7 @@ __device__ __forceinline__ uint32_t ticket_publish(PairSync &ps, uint32_t *ticke
 }
 __device__ __forceinline__ uint32_t ticket_consume(PairSync &ps, uint32_t T, int lane) {   // epilogue warp
     const uint32_t ts = T & 1u;
-    tc::mbar_wait(tc::smem_u32(&ps.tfull[ts]), (T >> 1) & 1u, 0x50000000u | T);
+    tc::mbar_wait<NGP_SLEEP_TICKET>(tc::smem_u32(&ps.tfull[ts]), (T >> 1) & 1u, 0x50000000u | T);
     const uint32_t t = *reinterpret_cast<volatile uint32_t *>(&ps.ticket[ts]);
     __syncwarp();
     if (lane == 0) tc::mbar_arrive(tc::smem_u32(&ps.tempty[ts]));
@@ -770,7 +798,7 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
         NGP_PROF(0)
         for (uint32_t i0 = 0; i0 < max_ne; i0 += K, P++) {
             const uint32_t slot = P & 1u;
-            tc::mbar_wait(ps_s + kEmpty + slot * 8u, (P >> 1) & 1u, 0x10000000u | P);   // layer 0 of pass P - 2 has consumed this slot
+            tc::mbar_wait<NGP_SLEEP_SLOT>(ps_s + kEmpty + slot * 8u, (P >> 1) & 1u, 0x10000000u | P);   // layer 0 of pass P - 2 has consumed this slot
             tc::fence_after_sync();
             NGP_PROF(5)
             const uint32_t i = i0 + my_k;
@@ -865,7 +893,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
 #ifndef NGP_ABLATE_MLP
 #pragma unroll 1
             for (int step = 0; step < n_all; step++) {
-                tc::mbar_wait(ps_s + kDfull, par, 0x30000000u | ((uint32_t)step << 24) | P);
+                tc::mbar_wait<NGP_SLEEP_LAYER>(ps_s + kDfull, par, 0x30000000u | ((uint32_t)step << 24) | P);
                 par ^= 1u;
                 tc::fence_after_sync();
                 NGP_PROF(6)

@@ -78,24 +78,32 @@ __device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier
 #ifdef NGP_WATCHDOG
 __device__ int g_wd_abort;
 #endif
+__device__ __forceinline__ bool mbar_try(uint32_t mbar_saddr, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"   // %3: suspend-time hint
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(done)
+        : "r"(mbar_saddr), "r"(parity), "r"(0x989680u)
+        : "memory");
+    return done != 0;
+}
+// kSleepNs: how long to stay off the issue port between two looks at the barrier.  The hardware's own suspension (the hint above) is
+// woken by ANY barrier traffic of the CTA -- with sixteen pipelines per SM that was ~40 wake-ups per wait, 10 % of all instructions
+// the kernel executed -- so a waiter that expects a long wait sleeps on the timer instead.
+template <uint32_t kSleepNs = 0>
 __device__ __forceinline__ void mbar_wait(uint32_t mbar_saddr, uint32_t parity, uint32_t info = 0) {
-    uint32_t done = 0;
 #ifdef NGP_WATCHDOG
     uint32_t spins = 0;
     const long long t0 = clock64();
 #endif
-    do {
-        asm volatile(
-            "{\n\t"
-            ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"   // %3: suspend-time hint -- sleep in hardware, do not poll
-            "selp.u32 %0, 1, 0, p;\n\t"
-            "}\n"
-            : "=r"(done)
-            : "r"(mbar_saddr), "r"(parity), "r"(0x989680u)
-            : "memory");
+    while (!mbar_try(mbar_saddr, parity)) {
+        if (kSleepNs) __nanosleep(kSleepNs);
 #ifdef NGP_WATCHDOG
-        if (!done && (++spins & 255u) == 0u) {
+        if ((++spins & 255u) == 0u) {
             if (*reinterpret_cast<volatile int *>(&g_wd_abort)) break;
             if (clock64() - t0 > 4000000000ll) {
                 atomicExch(&g_wd_abort, 1);
@@ -107,7 +115,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t mbar_saddr, uint32_t parity, 
 #else
         (void)info;
 #endif
-    } while (!done);
+    }
 }
 
 // ---- tensor memory

@@ -149,6 +149,24 @@ int ngp_density_forward(ngp_ctx *ctx, const float *xyzs, uint32_t M, int apply_d
 int ngp_render(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma,
                uint32_t max_steps, float bg_color, float *image, float *depth, float *weights_sum,
                int32_t *samples_per_ray, int64_t *stats, void *stream);
+/* ngp_render with the per-ray / per-sample outputs the reference's uncertainty-quantification callers read (uncertain.py:80-91,
+ * 185-189; nerf/renderer.py:244, 381-384), all optional (NULL = not wanted):
+ *   aggregated_density [N] fp32     sum over the ray's samples of weight * sigma (renderer.py:244, which only the sampler path
+ *                                   `run()` computes upstream)
+ *   sample_dump [dump_rows][4] fp32 (sigma * density_scale, r, g, b) of EVERY sample the LAST epoch evaluated, at the sample's row of
+ *                                   the epoch's sample buffer; dump_rows >= ngp_render_sample_rows(ctx, N).  With it:
+ *   ray_info [N][4] int32           by ray id: (epoch tag, position in that epoch's live list, samples marched in it, iteration of
+ *                                   the epoch in which the ray fell below T = 1e-4 or INT_MAX)
+ *   dump_header [8] int64           of the last epoch: its tag, n_step, reference iterations it ran, log2 K, row slots per ray,
+ *                                   live rays at its start, samples per ray, 0.  Sample i of live-list position n sits at row
+ *                                   (n / R) * R * slots + (i / K) * 32 + (n % R) * K + i % K with R = 32 / K.
+ * nerfsafetyvalidation_b200/nerf/renderer.py assembles the reference's `sigmas` / `rgbs` (its last iteration's tensors) from these. */
+int ngp_render_uq(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma,
+                  uint32_t max_steps, float bg_color, float *image, float *depth, float *weights_sum,
+                  int32_t *samples_per_ray, int64_t *stats, float *aggregated_density, float *sample_dump,
+                  uint64_t dump_rows, int32_t *ray_info, int64_t *dump_header, void *stream);
+/* Rows of the epoch sample buffer a render of N rays uses (HOST out): the size sample_dump must have. */
+int ngp_render_sample_rows(ngp_ctx *ctx, uint32_t N, uint64_t *rows);
 /* Same, HOST buffers in and out: H2D of rays, render, D2H of image/depth; synchronous.  This is the call the
  * end-to-end number in bench.py is measured through. */
 int ngp_render_host(ngp_ctx *ctx, const float *rays_o_host, const float *rays_d_host, uint32_t N,

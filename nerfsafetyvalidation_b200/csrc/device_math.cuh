@@ -215,14 +215,17 @@ __device__ __forceinline__ uint32_t march_ray(const MarchConst &m, float ox, flo
 struct RayAcc {
     float t, ws, d, r, g, b;
 };
+// w_out (optional): the sample's compositing weight alpha * T, for per-ray sums the reference's sampler path keeps
+// (aggregated_density = sum of w * sigma, nerf/renderer.py:244).
 __device__ __forceinline__ bool composite_sample(RayAcc &a, float sigma, float cr, float cg, float cb, float dt,
-                                                 float delta_t) {
+                                                 float delta_t, float *w_out = nullptr) {
     const float q = __fmul_rn(__fmul_rn(dt, sigma), -1.4426950216293334961f);
     float e;
     asm("ex2.approx.f32 %0, %1;" : "=f"(e) : "f"(q));  // __expf(-sigma*dt)
     const float alpha = __fsub_rn(1.0f, e);
     const float T = __fsub_rn(1.0f, a.ws);
     const float w = __fmul_rn(alpha, T);
+    if (w_out) *w_out = w;
     a.ws = __fadd_rn(a.ws, w);
     a.t = __fadd_rn(a.t, delta_t);
     a.d = __fmaf_rn(w, a.t, a.d);

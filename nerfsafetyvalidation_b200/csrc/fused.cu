@@ -535,6 +535,13 @@ struct RenderArgs {
     int *samples_per_ray;
     long long *stats;
     long long *prof;   // optional [8]: warp-cycles per phase (diagnostics, ngp_ctx_phase_cycles)
+    // ---- optional outputs for uncertainty quantification (ngp_render_uq; all NULL in ngp_render)
+    float *agg[2];           // [N] per buffer: sum of w * sigma per ray, committed / tentative like `state`
+    float *agg_out;          // [N] aggregated_density (nerf/renderer.py:244)
+    float4 *dump;            // [dump_rows] (sigma, r, g, b) of every sample of the CURRENT epoch at its sample-buffer row
+    uint32_t dump_rows;
+    int4 *ray_info;          // [N] by ray id: (seq of the epoch that last evaluated the ray, live-list position, samples, T-death iteration)
+    long long *dump_hdr;     // [8] of the last committed epoch: seq, s, iterations run, log2 K, row slots per ray, n_alive, samples per ray, 0
 };
 
 __device__ __forceinline__ uint32_t clamp_n_step(uint32_t N, uint32_t n_alive) {   // renderer.py:357
@@ -803,7 +810,7 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
             NGP_PROF(5)
             const uint32_t i = i0 + my_k;
             const unsigned long long dw = *dead_w;
-            const bool dead = (uint32_t)(dw >> 32) == tile + 1u && (((uint32_t)dw >> lane) & 1u);
+            const bool dead = ra.dump == nullptr && (uint32_t)(dw >> 32) == tile + 1u && (((uint32_t)dw >> lane) & 1u);   // a dump wants every marched sample
             const bool active = has_ray && i < ne && !dead;
             const float t = t_next;
             if (!dead && i + K < ne) t_next = __ldcg(reinterpret_cast<const float *>(ra.smp + tbase + (i0 + K) * R));
@@ -836,7 +843,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                                               float4 *scratch, int lane, int q, uint32_t lt_mask,
                                               const int *__restrict__ alive_in, int *__restrict__ alive_out, const float4 *__restrict__ state_in,
                                               float4 *__restrict__ state_out, uint32_t n_alive, uint32_t s, uint32_t ES, const TileGeom tg,
-                                              uint32_t seq, EpochCtr *ec, uint32_t *s_hist, uint32_t &P, uint32_t &T, uint32_t &par, long long (&pc)[8]) {
+                                              uint32_t seq, uint32_t agg_in, EpochCtr *ec, uint32_t *s_hist, uint32_t &P, uint32_t &T, uint32_t &par, long long (&pc)[8]) {
     const uint32_t kshift = tg.kshift, K = 1u << kshift, R = 32u >> kshift;
     const uint32_t n_tiles = (n_alive + R - 1) / R;
     const uint32_t my_r = (uint32_t)lane >> kshift, my_k = (uint32_t)lane & (K - 1u);
@@ -863,7 +870,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
         int index = 0;
         // The accumulators of a ray live in SHARED memory between passes (3 x 16 B in its leader lane's slot): only the leader lanes touch
         // them, for a few instructions per pass, and keeping them out of the register file is what keeps the layer loop free of spills.
-        //   rs[0] = (t, weights_sum, depth, samples)   rs[1] = (r, g, b, death)   rs[2] = (chunk, in_chunk, -, -)
+        //   rs[0] = (t, weights_sum, depth, samples)   rs[1] = (r, g, b, death)   rs[2] = (chunk, in_chunk, sum of w * sigma, T-death iteration)
         if (has_ray) {
             ne = min(__ldcg(ra.n_emit + n), ES);
             index = __ldcg(alive_in + n);
@@ -873,7 +880,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                 const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
                 rs[0] = make_float4(r0.x, r0.y, r0.z, r1.w);
                 rs[1] = make_float4(r1.x, r1.y, r1.z, 0.f);
-                rs[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+                rs[2] = make_float4(0.f, 0.f, ra.agg_out ? __ldcg(ra.agg[agg_in] + index) : 0.f, __uint_as_float(0x7fffffffu));
             }
         }
         uint32_t max_ne = ne;
@@ -940,6 +947,10 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                     issue_layer0(nc, tmem_col, w_desc, nslot, q, ps_s + kEmpty + nslot * 8u, ps_s + kDfull);
             }
 #endif
+            if (ra.dump != nullptr && has_ray && i < ne) {   // opt-in: the per-sample outputs uncertain.py-style callers read (renderer.py:381-384)
+                const uint32_t row = tbase + i0 * R;
+                if (row < ra.dump_rows) __stcs(ra.dump + row, make_float4(sg, cr, cg, cbl));
+            }
             const float dt = sample_dt(ra.mc, sc.x);
             if (K > 1) {
                 scr[0] = make_float4(sg, cr, cg, cbl);
@@ -950,13 +961,19 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                 const float4 s0 = rs[0], s1 = rs[1], s2 = rs[2];
                 RayAcc a = {s0.x, s0.y, s0.z, s1.x, s1.y, s1.z};
                 uint32_t samples = __float_as_uint(s0.w), death = __float_as_uint(s1.w), chunk = __float_as_uint(s2.x), in_chunk = __float_as_uint(s2.y);
+                float agg = s2.z;
+                uint32_t t_death = __float_as_uint(s2.w);
                 const uint32_t cnt = min(K, ne - i0);
                 for (uint32_t k = 0; k < cnt; k++) {
                     float4 o = make_float4(sg, cr, cg, cbl), dd = make_float4(dt, sc.y, 0.f, 0.f);
                     if (K > 1) { o = scr[2 * k]; dd = scr[2 * k + 1]; }
-                    if (composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y)) {
+                    float w;
+                    const bool done = composite_sample(a, o.x, o.y, o.z, o.w, dd.x, dd.y, &w);
+                    agg = __fmaf_rn(w, o.x, agg);   // renderer.py:244: aggregated_density = sum(weights * sigma)
+                    if (done) {
                         dead = true;
                         death = chunk;
+                        t_death = chunk;
                         samples += min(ne, (chunk + 1) * s);   // the reference marched the whole chunk before compositing it
                         break;
                     }
@@ -964,7 +981,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
                 }
                 rs[0] = make_float4(a.t, a.ws, a.d, __uint_as_float(samples));
                 rs[1] = make_float4(a.r, a.g, a.b, __uint_as_float(death));
-                rs[2] = make_float4(__uint_as_float(chunk), __uint_as_float(in_chunk), 0.f, 0.f);
+                rs[2] = make_float4(__uint_as_float(chunk), __uint_as_float(in_chunk), agg, __uint_as_float(t_death));
             }
             if (K > 1) dead = __shfl_sync(0xffffffffu, dead, lead_lane);
             {   // tell the gather warp which rows it may skip from now on (a hint: a stale or foreign word only costs work)
@@ -989,6 +1006,8 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
             float4 *so = state_out + 2 * (size_t)index;
             __stcg(so, make_float4(a.t, a.ws, a.d, __uint_as_float(seq)));
             __stcg(so + 1, make_float4(a.r, a.g, a.b, __uint_as_float(samples)));
+            if (ra.agg_out) __stcg(ra.agg[agg_in ^ 1] + index, rs[2].z);
+            if (ra.ray_info) __stcg(ra.ray_info + index, make_int4((int)seq, (int)n, (int)ne, (int)__float_as_uint(rs[2].w)));
         }
         const uint32_t ballot = __ballot_sync(0xffffffffu, survives);   // renderer.py:369
         if (ballot) {
@@ -1070,6 +1089,8 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         ra.state[0][2 * (size_t)n] = make_float4(near, 0.f, 0.f, __uint_as_float(1u));
         ra.state[0][2 * (size_t)n + 1] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
         ra.state[1][2 * (size_t)n] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+        if (ra.agg_out) ra.agg[0][n] = 0.f;
+        if (ra.ray_info) ra.ray_info[n] = make_int4(0, 0, 0, 0);
     }
     grid.sync();
 
@@ -1158,7 +1179,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         } else {
             set_max_regs_dec<NGP_EPI_REGS>();
             epilogue_role<kProf>(nc, ra, ss, tmem_col, w_desc, s_scratch + (size_t)(warp - kGatherWarps) * kScratchPerWarp, lane, q, lt_mask, alive_in,
-                                 alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, ec, s_hist, passes, tiles, par, pc);
+                                 alive_out, state_in, state_out, n_alive, s, ES, tg, attempt + 2, in, ec, s_hist, passes, tiles, par, pc);
             set_max_regs_inc<NGP_EPI_REGS ? 64 : 0>();
         }
         if (kProf) g0 = clock64();
@@ -1194,6 +1215,11 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
             continue;
         }
         if (blockIdx.x == 0 && tid == 0 && __ldcg(&ec->n_out) != na) ra.ctr->error = 1;   // histogram and live list disagree
+        if (ra.dump_hdr && blockIdx.x == 0 && tid == 0) {   // this epoch is committed: it is the last one so far
+            ra.dump_hdr[0] = (long long)(attempt + 1u); ra.dump_hdr[1] = (long long)s; ra.dump_hdr[2] = (long long)ran;
+            ra.dump_hdr[3] = (long long)tg.kshift; ra.dump_hdr[4] = (long long)tg.ESp; ra.dump_hdr[5] = (long long)n_alive;
+            ra.dump_hdr[6] = (long long)ES; ra.dump_hdr[7] = 0;
+        }
         replay = false;
         step += ran * s;
         iter += ran;
@@ -1228,6 +1254,7 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         float *im = ra.image + (size_t)n * 3;
         im[0] = __fadd_rn(r1.x, k); im[1] = __fadd_rn(r1.y, k); im[2] = __fadd_rn(r1.z, k);
         ra.weights_sum[n] = ws_n;
+        if (ra.agg_out) ra.agg_out[n] = __ldcg(ra.agg[second ? 1 : 0] + n);
         const float near = ra.nears[n], far = ra.fars[n];
         const float dd = __fsub_rn(r0.z, near);
         ra.depth[n] = __fdiv_rn(dd < 0.f ? 0.f : dd, __fsub_rn(far, near));   // 0/0 = NaN for misses, like the reference
@@ -1284,6 +1311,8 @@ struct ngp_ctx {
     float2 *smp = nullptr;
     float4 *state[2] = {nullptr, nullptr};
     RenderOptions opt;
+    float *agg[2] = {nullptr, nullptr};   // aggregated-density accumulators (ngp_render_uq), allocated on first use
+    uint32_t capAgg = 0;
     uint32_t *h_error = nullptr;  // pinned host word: RenderCtr::error of the last *_host render
     uint32_t *n_emit = nullptr;
     int *alive[2] = {nullptr, nullptr};
@@ -1332,7 +1361,7 @@ int ngp_ctx_create(ngp_ctx **out) {
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
     cudaFree(c->wpack); cudaFree(c->wtc); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
-    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp);
+    cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp); cudaFree(c->agg[0]); cudaFree(c->agg[1]);
     if (c->h_error) cudaFreeHost(c->h_error);
     cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws); cudaFree(c->d_poses);
     delete c;
@@ -1536,8 +1565,53 @@ static int ensure_workspace(ngp_ctx *c, uint32_t N) {
     return 0;
 }
 
+struct RenderExtras {   // ngp_render_uq's optional outputs
+    float *aggregated_density = nullptr;
+    float *sample_dump = nullptr;
+    uint32_t dump_rows = 0;
+    int32_t *ray_info = nullptr;
+    int64_t *dump_header = nullptr;
+};
+static int render_core(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps, float bg_color,
+                       float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, const RenderExtras &ex, void *stream);
+
 int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps, float bg_color,
                float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, void *stream) {
+    return render_core(c, rays_o, rays_d, N, dt_gamma, max_steps, bg_color, image, depth, weights_sum, samples_per_ray, stats, RenderExtras(), stream);
+}
+
+int ngp_render_sample_rows(ngp_ctx *c, uint32_t N, uint64_t *rows) {
+    NGP_REQUIRE(c != nullptr && rows != nullptr, "render_sample_rows: null argument");
+    unsigned long long rpr = c->opt.rows_per_ray < 3u ? 3u : c->opt.rows_per_ray;
+    const uint32_t cap = N <= c->capN ? c->capN : N + N / 8 + 1024;
+    unsigned long long r = rpr * cap + 1024;
+    *rows = r > 0x7fffffffull ? 0x7fffffffull : r;
+    return 0;
+}
+
+int ngp_render_uq(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps, float bg_color,
+                  float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, float *aggregated_density,
+                  float *sample_dump, uint64_t dump_rows, int32_t *ray_info, int64_t *dump_header, void *stream) {
+    NGP_REQUIRE(c != nullptr, "render_uq: null ctx");
+    RenderExtras ex;
+    if (aggregated_density) { NGP_DEVPTR(aggregated_density); ex.aggregated_density = aggregated_density; }
+    if (sample_dump) {
+        NGP_DEVPTR(sample_dump); NGP_DEVPTR(ray_info); NGP_DEVPTR(dump_header);
+        ex.sample_dump = sample_dump; ex.dump_rows = dump_rows > 0x7fffffffull ? 0x7fffffffu : (uint32_t)dump_rows;
+        ex.ray_info = ray_info; ex.dump_header = dump_header;
+    }
+    if (N && ex.aggregated_density && N > c->capAgg) {
+        free_all(c->agg[0], c->agg[1]);
+        c->capAgg = 0;
+        NGP_CUDA(cudaMalloc(&c->agg[0], sizeof(float) * (size_t)N));
+        NGP_CUDA(cudaMalloc(&c->agg[1], sizeof(float) * (size_t)N));
+        c->capAgg = N;
+    }
+    return render_core(c, rays_o, rays_d, N, dt_gamma, max_steps, bg_color, image, depth, weights_sum, samples_per_ray, stats, ex, stream);
+}
+
+static int render_core(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps, float bg_color,
+                       float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, const RenderExtras &ex, void *stream) {
     NGP_REQUIRE(c != nullptr && c->has_net && c->has_scene, "render: ngp_ctx_set_network / ngp_ctx_set_scene have not been called");
     NGP_REQUIRE(max_steps >= 1, "render: max_steps must be >= 1");
     NGP_REQUIRE(c->fast_levels, "render: a hash-grid level is neither a dense grid that fits its table nor a power-of-two hash table; "
@@ -1574,6 +1648,9 @@ int ngp_render(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N,
     ra.horizon_div = (float)(op.horizon_div < 1u ? 1u : op.horizon_div);
     ra.ctr = c->ctr; ra.image = image; ra.depth = depth; ra.weights_sum = weights_sum;
     ra.samples_per_ray = samples_per_ray; ra.stats = reinterpret_cast<long long *>(stats); ra.prof = c->prof;
+    ra.agg[0] = c->agg[0]; ra.agg[1] = c->agg[1]; ra.agg_out = ex.aggregated_density;
+    ra.dump = reinterpret_cast<float4 *>(ex.sample_dump); ra.dump_rows = ex.dump_rows;
+    ra.ray_info = reinterpret_cast<int4 *>(ex.ray_info); ra.dump_hdr = reinterpret_cast<long long *>(ex.dump_header);
     ra.coarse = nullptr; ra.coarse_words = 0;
     size_t smem = c->render_smem;
     if (!op.no_coarse && c->coarse_words && smem + (NGP_COARSE_SMEM ? c->coarse_words * 4 : 0) <= c->render_smem_max) {

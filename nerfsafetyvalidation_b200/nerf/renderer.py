@@ -224,7 +224,7 @@ class NeRFRenderer(nn.Module):
             ctx_owner.keys = dict(ctx_owner.keys or {}, scene=key)
 
     def run_cuda(self, rays_o, rays_d, dt_gamma=0, bg_color=None, perturb=False, force_all_rays=False, max_steps=1024,
-                 fused=None, return_stats=False, **kwargs):
+                 fused=None, return_stats=False, return_uq=False, **kwargs):
         """nerf/renderer.py:261-386, inference branch.  rays_o, rays_d: [B, N, 3] -> dict(image [B,N,3], depth [B,N], ...)."""
         if self.training:
             raise NotImplementedError("run_cuda: the training branch (march_rays_train / composite_rays_train) is outside the "
@@ -242,30 +242,77 @@ class NeRFRenderer(nn.Module):
         fused = self.fused if fused is None else fused
         scalar_bg = not torch.is_tensor(bg_color)
         if fused and not perturb and scalar_bg and self._configure_native(self._native):
-            return self._run_fused(rays_o, rays_d, prefix, N, device, float(dt_gamma), int(max_steps), float(bg_color), return_stats)
+            return self._run_fused(rays_o, rays_d, prefix, N, device, float(dt_gamma), int(max_steps), float(bg_color), return_stats,
+                                   return_uq)
         return self._run_stepwise(rays_o, rays_d, prefix, N, device, dt_gamma, bg_color, perturb, max_steps)
 
-    def _run_fused(self, rays_o, rays_d, prefix, N, device, dt_gamma, max_steps, bg_color, return_stats):
+    def _run_fused(self, rays_o, rays_d, prefix, N, device, dt_gamma, max_steps, bg_color, return_stats, return_uq=False):
         lib = _cabi.load()
         image = torch.empty(N, 3, dtype=torch.float32, device=device)
         depth = torch.empty(N, dtype=torch.float32, device=device)
         weights_sum = torch.empty(N, dtype=torch.float32, device=device)
         spr = torch.empty(N, dtype=torch.int32, device=device) if return_stats else None
         stats = torch.zeros(4, dtype=torch.int64, device=device) if return_stats else None
+        results = {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum,
+                   # the reference returns the LAST iteration's per-sample tensors (renderer.py:381-382); the fused loop only
+                   # materialises them on request (return_uq=True)
+                   "sigmas": None, "rgbs": None}
         with torch.cuda.device(device):   # the context, its workspace and the launch stream all belong to the tensors' device
             handle = self._native.get(device)
             self._set_scene(self._native, handle)
-            _cabi.check(lib.ngp_render(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
-                                       _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(spr), _cabi.ptr(stats),
-                                       _cabi.stream()), "ngp_render")
-        results = {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum,
-                   # the reference returns the LAST iteration's per-sample tensors (renderer.py:381-382); the fused loop
-                   # never materialises them
-                   "sigmas": None, "rgbs": None}
+            if not return_uq:
+                _cabi.check(lib.ngp_render(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
+                                           _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(spr), _cabi.ptr(stats),
+                                           _cabi.stream()), "ngp_render")
+            else:
+                rows = C.c_uint64()
+                _cabi.check(lib.ngp_render_sample_rows(handle, N, C.byref(rows)), "ngp_render_sample_rows")
+                agg = torch.empty(N, dtype=torch.float32, device=device)
+                dump = torch.empty(int(rows.value), 4, dtype=torch.float32, device=device)
+                info = torch.empty(N, 4, dtype=torch.int32, device=device)
+                hdr = torch.zeros(8, dtype=torch.int64, device=device)
+                _cabi.check(lib.ngp_render_uq(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
+                                              _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(spr), _cabi.ptr(stats),
+                                              _cabi.ptr(agg), _cabi.ptr(dump), int(rows.value), _cabi.ptr(info), _cabi.ptr(hdr),
+                                              _cabi.stream()), "ngp_render_uq")
+                results["aggregated_density"] = agg.view(*prefix)
+                results["sigmas"], results["rgbs"] = self._last_iteration_samples(dump, info, hdr)
         if return_stats:
             results["samples_per_ray"] = spr
             results["stats"] = stats
         return results
+
+    def _last_iteration_samples(self, dump, info, hdr):
+        """The reference's `sigmas` / `rgbs` result keys (renderer.py:357-365, 381-382): the network outputs of the LAST iteration
+        of its loop, row = (rank of the ray among the rays alive in that iteration, by ray id: the reference's compaction is
+        stable) * n_step + k, padded to a multiple of 128 rows (march_rays' `align`); rows the marcher did not fill hold the
+        network's output for xyz = dir = 0 (its buffers start as zeros).  Assembled from ngp_render_uq's per-sample dump of the
+        last epoch (include/ngp_b200.h)."""
+        tag, s, ran, kshift, slots, _, _, _ = (int(v) for v in hdr.cpu().tolist())
+        device = dump.device
+        zero = torch.zeros(1, 3, device=device)
+        sigma0, rgb0 = self(zero, zero)
+        sigma0 = float(self.density_scale) * sigma0.float()
+        if ran <= 0:
+            return None, None
+        j = ran - 1                                                 # the last iteration the reference ran, within the last epoch
+        K, R = 1 << kshift, 32 >> kshift
+        rid = torch.nonzero(info[:, 0] == tag).flatten()            # ascending ray id = the reference's live-list order
+        n, ne, t_death = (info[rid, c].long() for c in (1, 2, 3))
+        alive = (ne >= j * s) & (t_death >= j) if j > 0 else torch.ones_like(n, dtype=torch.bool)   # survived iterations 0 .. j-1
+        n, ne = n[alive], ne[alive]
+        M = n.numel() * s
+        padded = -(-M // 128) * 128 if M else 0
+        sigmas = sigma0.expand(padded).clone()
+        rgbs = rgb0.to(torch.float32).expand(padded, 3).clone()
+        if M:
+            i = j * s + torch.arange(s, device=device)[None, :]      # [rays, n_step] sample numbers within the epoch
+            row = (n // R)[:, None] * (R * slots) + (i >> kshift) * 32 + (n % R)[:, None] * K + (i & (K - 1))
+            valid = i < ne[:, None]
+            out = dump[row.clamp_(0, dump.shape[0] - 1)]
+            sigmas[:M] = torch.where(valid, out[..., 0], sigma0).reshape(-1)
+            rgbs[:M] = torch.where(valid[..., None], out[..., 1:], rgb0.to(torch.float32)).reshape(-1, 3)
+        return sigmas, rgbs
 
     def _run_stepwise(self, rays_o, rays_d, prefix, N, device, dt_gamma, bg_color, perturb, max_steps):
         with torch.no_grad():

@@ -57,6 +57,20 @@ int ngp_morton3D(const int32_t *coords, uint32_t N, int32_t *indices, void *stre
 int ngp_morton3D_invert(const int32_t *indices, uint32_t N, int32_t *coords, void *stream);
 /* raymarching/src/raymarching.cu:269-302.  N = number of output BYTES (C*H^3/8). */
 int ngp_packbits(const float *grid, uint32_t N, float density_thresh, uint8_t *bitfield, void *stream);
+/* Occupancy-grid maintenance (nerf/renderer.py:388-546), in the Morton order density_grid is stored in.
+ * ngp_occupancy_points: the query points of one cascade, xyz [n,3] fp32 =
+ *     ((2 c) / (H - 1) - 1) * (bound_c - bound_c / H) + (2 u - 1) * bound_c / H          (renderer.py:481-490, same roundings)
+ *   coords == NULL: n = H^3, point m = the cell with Morton index m, u = jitter row (x H + y) H + z (the row the reference's
+ *                   meshgrid enumeration gives that cell: the same random stream lands on the same cells);
+ *   coords int32 [n,3]: point i = cell coords[i], u = jitter row i (the partial-update branch, :497-523);
+ *   jitter fp32 [rows,3] in [0,1) or NULL (cell centres).
+ * ngp_density_grid_ema: grid = max(grid * decay, tmp) where both are >= 0 (:531-532), in place.
+ * ngp_mark_untrained_grid: density_grid[c][m] = -1 for every cell no pose (cam2world [B,4,4] fp32, device) sees (:388-449). */
+int ngp_occupancy_points(const int32_t *coords, const float *jitter, uint32_t n, uint32_t H, float bound_c,
+                         float *xyzs, void *stream);
+int ngp_density_grid_ema(float *grid, const float *tmp, uint32_t n, float decay, void *stream);
+int ngp_mark_untrained_grid(const float *poses, uint32_t B, float fx, float fy, float cx, float cy, uint32_t H,
+                            uint32_t cascade, float bound, float *density_grid, void *stream);
 /* raymarching/src/raymarching.cu:706-825.  xyzs/dirs/deltas must be pre-zeroed by the caller
  * (raymarching.py:329-331).  perturb must be 0 (validate.py:290 never perturbs at inference). */
 int ngp_march_rays(uint32_t n_alive, uint32_t n_step, const int32_t *rays_alive, const float *rays_t,

@@ -21,6 +21,9 @@ _SIGNATURES = {
     "ngp_morton3D": [_p, _u32, _p, _p],
     "ngp_morton3D_invert": [_p, _u32, _p, _p],
     "ngp_packbits": [_p, _u32, _f32, _p, _p],
+    "ngp_occupancy_points": [_p, _p, _u32, _u32, _f32, _p, _p],
+    "ngp_density_grid_ema": [_p, _p, _u32, _f32, _p],
+    "ngp_mark_untrained_grid": [_p, _u32, _f32, _f32, _f32, _f32, _u32, _u32, _f32, _p, _p],
     "ngp_march_rays": [_u32, _u32, _p, _p, _p, _p, _f32, _f32, _u32, _u32, _u32, _p, _p, _p, _p, _p, _p, _u32, _p],
     "ngp_composite_rays": [_u32, _u32, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "ngp_compact_scratch_bytes": [_u32],

@@ -15,7 +15,7 @@ CSRC = os.path.join(PKG, "csrc")
 OBJ = os.path.join(PKG, "_lib", "obj")
 LIB = os.path.join(PKG, "_lib", "libngp_b200.so")
 
-SOURCES = ["common.cu", "ops_raymarch.cu", "ops_encode.cu", "ops_mlp.cu", "fused.cu"]
+SOURCES = ["common.cu", "ops_raymarch.cu", "ops_encode.cu", "ops_mlp.cu", "ops_occupancy.cu", "fused.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

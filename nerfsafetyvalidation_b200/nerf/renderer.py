@@ -16,6 +16,7 @@ with our kernels for near/far and every network query; it is a convenience for c
 import ctypes as C
 import math
 
+import numpy as np
 import torch
 import torch.nn as nn
 
@@ -406,36 +407,75 @@ class NeRFRenderer(nn.Module):
 
     @torch.no_grad()
     def mark_untrained_grid(self, poses, intrinsic, S=64):
-        raise NotImplementedError("mark_untrained_grid belongs to training-time occupancy maintenance (SURVEY.md section 8f row 4)")
+        """nerf/renderer.py:388-449: density_grid = -1 for every cell that no training camera covers.  poses [B,4,4] cam2world,
+        intrinsic (fx, fy, cx, cy).  One kernel over (cascade, Morton cell) that walks the poses in registers
+        (ngp_mark_untrained_grid) instead of the reference's five nested Python loops; `S` (its block size) has no meaning here."""
+        if not self.cuda_ray:
+            return
+        if isinstance(poses, np.ndarray):
+            poses = torch.from_numpy(poses)
+        dev = self.density_bitfield.device
+        poses = poses.to(dev, torch.float32).contiguous()
+        fx, fy, cx, cy = (float(v) for v in intrinsic)
+        with torch.cuda.device(dev):
+            _cabi.check(_cabi.load().ngp_mark_untrained_grid(_cabi.ptr(poses), poses.shape[0], fx, fy, cx, cy, self.grid_size, self.cascade,
+                                                             float(self.bound), _cabi.ptr(self.density_grid), _cabi.stream()),
+                        "ngp_mark_untrained_grid")
+
+    def _cascade_sigmas(self, cas, coords, jitter):
+        """density * density_scale at the jittered query points of cascade `cas` (renderer.py:484-494): all cells in Morton order
+        (coords None) or the given cells."""
+        dev = self.density_bitfield.device
+        n = self.grid_size ** 3 if coords is None else coords.shape[0]
+        xyzs = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        bound_c = float(min(2 ** cas, self.bound))
+        _cabi.check(_cabi.load().ngp_occupancy_points(_cabi.ptr(coords), _cabi.ptr(jitter), n, self.grid_size, bound_c, _cabi.ptr(xyzs),
+                                                      _cabi.stream()), "ngp_occupancy_points")
+        sigmas = self.density(xyzs)["sigma"].reshape(-1).detach().float()
+        return sigmas * self.density_scale
 
     @torch.no_grad()
     def update_extra_state(self, decay=0.95, S=128):
-        """nerf/renderer.py:451-546, full-update branch: density query on the 128^3 x cascade grid (jittered cell centres),
-        EMA-max with the running grid, then `packbits` with thresh = min(mean_density, density_thresh)."""
+        """nerf/renderer.py:451-546.  The density grid lives in Morton order, so the update works in Morton order: per cascade ONE
+        kernel writes the jittered query point of every cell at its Morton index (ngp_occupancy_points), ONE density query
+        (ngp_density_forward) returns the cascade's row of the new grid -- no coordinate / index tensors, no scatter -- and the
+        EMA-max is one in-place pass (ngp_density_grid_ema).  The random numbers are drawn exactly as the reference draws them (one
+        torch.rand per S^3 block per cascade, in its loop order), so that a seeded call reproduces its grid."""
         if not self.cuda_ray:
             return
         dev = self.density_bitfield.device
-        tmp_grid = -torch.ones_like(self.density_grid)
-        ar = torch.arange(self.grid_size, dtype=torch.int32, device=dev)
-        for xs in ar.split(S):
-            for ys in ar.split(S):
-                for zs in ar.split(S):
-                    xx, yy, zz = torch.meshgrid(xs, ys, zs, indexing="ij")
-                    coords = torch.cat([xx.reshape(-1, 1), yy.reshape(-1, 1), zz.reshape(-1, 1)], dim=-1)
-                    indices = raymarching.morton3D(coords).long()
-                    xyzs = 2 * coords.float() / (self.grid_size - 1) - 1
-                    for cas in range(self.cascade):
-                        bound = min(2 ** cas, self.bound)
-                        half_grid_size = bound / self.grid_size
-                        cas_xyzs = xyzs * (bound - half_grid_size)
-                        cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * half_grid_size
-                        sigmas = self.density(cas_xyzs)["sigma"].reshape(-1).detach().float()
-                        sigmas *= self.density_scale
-                        tmp_grid[cas, indices] = sigmas
-        valid_mask = (self.density_grid >= 0) & (tmp_grid >= 0)
-        self.density_grid[valid_mask] = torch.maximum(self.density_grid[valid_mask] * decay, tmp_grid[valid_mask])
-        self.mean_density = torch.mean(self.density_grid.clamp(min=0)).item()
-        self.iter_density += 1
-        density_thresh = min(self.mean_density, self.density_thresh)
-        self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
+        H, n_cas = self.grid_size, self.cascade
+        lib = _cabi.load()
+        with torch.cuda.device(dev):
+            tmp_grid = torch.full_like(self.density_grid, -1.0)
+            if self.iter_density < 16:                                           # full update (renderer.py:466-494)
+                jitter = torch.empty(n_cas, H, H, H, 3, dtype=torch.float32, device=dev)
+                cuts = [(h, min(h + S, H)) for h in range(0, H, S)]
+                for x0, x1 in cuts:                                              # the reference's consumption order of the generator
+                    for y0, y1 in cuts:
+                        for z0, z1 in cuts:
+                            for cas in range(n_cas):
+                                jitter[cas, x0:x1, y0:y1, z0:z1] = torch.rand((x1 - x0) * (y1 - y0) * (z1 - z0), 3, device=dev).view(
+                                    x1 - x0, y1 - y0, z1 - z0, 3)
+                for cas in range(n_cas):
+                    tmp_grid[cas] = self._cascade_sigmas(cas, None, jitter[cas].reshape(-1, 3))
+            else:                                                                # partial update (renderer.py:497-523)
+                N = H ** 3 // 4
+                for cas in range(n_cas):
+                    coords = torch.randint(0, H, (N, 3), device=dev)
+                    occ = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
+                    occ = occ[torch.randint(0, occ.shape[0], [N], dtype=torch.long, device=dev)]   # duplicates allowed
+                    coords = torch.cat([coords.int(), raymarching.morton3D_invert(occ)], dim=0).contiguous()
+                    indices = torch.cat([raymarching.morton3D(coords[:N]).long(), occ], dim=0)
+                    jitter = torch.rand(2 * N, 3, device=dev)
+                    tmp_grid[cas, indices] = self._cascade_sigmas(cas, coords, jitter)
+            _cabi.check(lib.ngp_density_grid_ema(_cabi.ptr(self.density_grid), _cabi.ptr(tmp_grid), tmp_grid.numel(), float(decay),
+                                                 _cabi.stream()), "ngp_density_grid_ema")
+            self.mean_density = torch.mean(self.density_grid.clamp(min=0)).item()   # -1 (never trained) counts as empty
+            self.iter_density += 1
+            density_thresh = min(self.mean_density, self.density_thresh)
+            self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
+        total_step = min(16, self.local_step)                                    # step-counter bookkeeping (renderer.py:540-544)
+        if total_step > 0:
+            self.mean_count = int(self.step_counter[:total_step, 0].sum().item() / total_step)
         self.local_step = 0

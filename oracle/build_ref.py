@@ -67,10 +67,26 @@ def build(name: str) -> str:
     return dst
 
 
+# The reference's own Python on the path, unmodified, so that the GPU box (which has no /root/reference) can run its methods on the
+# rebuilt extensions: tests/refext.reference_renderer_class() imports nerf/renderer.py from here behind three stub modules.  Like the
+# .so files these are build OUTPUTS: oracle/_ref/ is git-ignored, nothing of it enters the repository's history.
+PYREF = ["nerf/renderer.py"]
+
+
+def copy_python():
+    dst_root = os.path.join(OUT, "pyref")
+    for rel in PYREF:
+        dst = os.path.join(dst_root, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copyfile(os.path.join(REF, rel), dst)
+    print("[build_ref] ->", dst_root, flush=True)
+
+
 def main(argv):
     if not os.path.isdir(REF):
         print(f"[build_ref] {REF} not present (GPU box?) - using prebuilt oracle/_ref if any")
         return 0
+    copy_python()
     names = argv or list(EXTS)
     for n in names:
         if not n.startswith("_"):

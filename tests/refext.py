@@ -127,6 +127,42 @@ def ffmlp(inputs, weights_f16, input_dim, output_dim, hidden_dim, num_layers):
     return outputs[:B, :output_dim]
 
 
+def reference_renderer_class():
+    """The reference's OWN nerf/renderer.py::NeRFRenderer (copied unmodified to oracle/_ref/pyref by oracle/build_ref.py),
+    imported behind three stubs: `raymarching` = the wrappers above on the rebuilt extension, `trimesh` (export_mesh only) and
+    `nerf.utils.custom_meshgrid`.  None when the copy is not there."""
+    import sys
+    import types
+    path = os.path.join(REF_DIR, "pyref", "nerf", "renderer.py")
+    if not os.path.exists(path) or not available("_raymarching"):
+        return None
+    if "ngp_ref_nerf.renderer" in sys.modules:
+        return sys.modules["ngp_ref_nerf.renderer"].NeRFRenderer
+    rm = types.ModuleType("raymarching")
+    rm.near_far_from_aabb, rm.morton3D, rm.morton3D_invert = near_far_from_aabb, morton3D, morton3D_invert
+    rm.march_rays, rm.composite_rays = march_rays, composite_rays
+    rm.packbits = lambda grid, thresh, bitfield=None: packbits(grid, thresh)   # raymarching.py:129-155 (allocates when None)
+    utils = types.ModuleType("ngp_ref_nerf.utils")
+    utils.custom_meshgrid = lambda *a: torch.meshgrid(*a, indexing="ij")       # nerf/utils.py:28-33
+    pkg = types.ModuleType("ngp_ref_nerf")
+    pkg.__path__ = [os.path.dirname(path)]
+    saved = {k: sys.modules.get(k) for k in ("raymarching", "trimesh")}
+    sys.modules.update({"raymarching": rm, "trimesh": saved["trimesh"] or types.ModuleType("trimesh"), "ngp_ref_nerf": pkg,
+                        "ngp_ref_nerf.utils": utils})
+    try:
+        spec = importlib.util.spec_from_file_location("ngp_ref_nerf.renderer", path)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["ngp_ref_nerf.renderer"] = mod
+        spec.loader.exec_module(mod)
+    finally:
+        for k, v in saved.items():   # the stubs stay bound inside the imported module; the process-wide names are restored
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    return mod.NeRFRenderer
+
+
 class RefModel:
     """Holds what network_ff.NeRFNetwork holds, as device tensors (half copies = what autocast would produce)."""
 
@@ -142,6 +178,12 @@ class RefModel:
         self.cascade, self.grid_size, self.min_near = cascade, grid_size, min_near
         b = self.bound
         self.aabb = torch.tensor([-b, -b, -b, b, b, b], dtype=torch.float32, device=device)
+
+    def density(self, x):
+        """network_ff.py:76-89 under autocast: {'sigma': exp(h0) fp32} (geo_feat is not needed by the occupancy update)."""
+        x01 = (x + self.bound) / (2 * self.bound)
+        h = ffmlp(grid_encode(x01, self.table, self.offsets, self.per_level_scale), self.w_sigma, 32, 16, 64, self.num_layers)
+        return {"sigma": torch.exp(h[..., 0].float())}
 
     def forward(self, x, d):
         """network_ff.py:51-74 under autocast."""

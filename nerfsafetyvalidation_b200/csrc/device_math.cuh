@@ -57,6 +57,24 @@ __device__ __forceinline__ bool slab_near_far(float ox, float oy, float oz, floa
 }
 
 // ------------------------------------------------------------------------------------------------
+// Camera ray of pixel p (row-major, H x W) of frame pose P (cam2world [4,4] row-major): nerf/utils.py:52-116 with N = -1 (every
+// pixel, centre at +0.5): direction ((i - cx) / fx, (j - cy) / fy, 1) normalised and rotated, origin = translation.  Operation order
+// is fixed (IEEE mul / add / div / sqrt, no contraction) so that ngp_get_rays, the renderer's prologue and the oracle agree bit for bit.
+__device__ __forceinline__ void pose_ray(const float *__restrict__ P, uint32_t p, uint32_t W, float fx, float fy, float cx, float cy, float (&o)[3],
+                                         float (&d)[3]) {
+    const float i = __fadd_rn((float)(p % W), 0.5f), j = __fadd_rn((float)(p / W), 0.5f);
+    const float x = __fdiv_rn(__fsub_rn(i, cx), fx), y = __fdiv_rn(__fsub_rn(j, cy), fy);
+    const float nrm = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), 1.0f));
+    const float d0 = __fdiv_rn(x, nrm), d1 = __fdiv_rn(y, nrm), d2 = __fdiv_rn(1.0f, nrm);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float r0 = __ldg(P + 4 * k), r1 = __ldg(P + 4 * k + 1), r2 = __ldg(P + 4 * k + 2);
+        d[k] = __fadd_rn(__fadd_rn(__fmul_rn(d0, r0), __fmul_rn(d1, r1)), __fmul_rn(d2, r2));
+        o[k] = __ldg(P + 4 * k + 3);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Occupancy-bitfield marcher (raymarching.cu:706-814)
 struct MarchConst {
     float bound, dt_gamma, dt_min, dt_max;

@@ -506,6 +506,13 @@ struct RenderOptions {
 
 struct RenderArgs {
     const float *rays_o, *rays_d;
+    // rays from camera poses (ngp_render_poses*): when `poses` is set, the prologue computes the ray of every pixel itself (nerf/utils.py:
+    // 52-116) and writes it to gen_o / gen_d (== rays_o / rays_d, the context's staging buffers) on its way to near / far -- no separate
+    // ray-generation launch, no second pass over the rays
+    const float *poses;
+    float *gen_o, *gen_d;
+    uint32_t img_w, img_hw;
+    float fx, fy, cx, cy;
     uint32_t N;
     float min_near, bg_color;
     uint32_t max_steps;
@@ -585,8 +592,8 @@ __device__ __forceinline__ void march_phase(const RenderArgs &ra, const uint32_t
                     n = my;
                     const int index = __ldcg(alive_in + n);
                     const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
-                    ox = __ldg(o); oy = __ldg(o + 1); oz = __ldg(o + 2);
-                    rd = make_ray_dir(__ldg(d), __ldg(d + 1), __ldg(d + 2));
+                    ox = __ldcg(o); oy = __ldcg(o + 1); oz = __ldcg(o + 2);   // L2: the prologue may have written the rays (poses)
+                    rd = make_ray_dir(__ldcg(d), __ldcg(d + 1), __ldcg(d + 2));
                     tm = __ldcg(reinterpret_cast<const float *>(state_in + 2 * (size_t)index));   // rays_t
                     last_t = tm; acc_t = tm;
                     far = __ldcg(ra.fars + index);
@@ -793,8 +800,8 @@ __device__ __forceinline__ void gather_role(const NetConst &nc, const RenderArgs
             ne = min(__ldcg(ra.n_emit + n), ES);   // ES may be shorter than what was marched (pre-validated epoch)
             const int index = __ldcg(alive_in + n);
             const float *o = ra.rays_o + (size_t)index * 3, *d = ra.rays_d + (size_t)index * 3;
-            ox = __ldg(o); oy = __ldg(o + 1); oz = __ldg(o + 2);
-            dx = __ldg(d); dy = __ldg(d + 1); dz = __ldg(d + 2);
+            ox = __ldcg(o); oy = __ldcg(o + 1); oz = __ldcg(o + 2);
+            dx = __ldcg(d); dy = __ldcg(d + 1); dz = __ldcg(d + 2);
         }
         uint32_t max_ne = ne;
 #pragma unroll
@@ -875,7 +882,7 @@ __device__ __forceinline__ void epilogue_role(const NetConst &nc, const RenderAr
             ne = min(__ldcg(ra.n_emit + n), ES);
             index = __ldcg(alive_in + n);
             const float *d = ra.rays_d + (size_t)index * 3;
-            sh_to_half(__ldg(d), __ldg(d + 1), __ldg(d + 2), shs[0], shs[1]);   // the direction is constant along the ray: SH once per tile,
+            sh_to_half(__ldcg(d), __ldcg(d + 1), __ldcg(d + 2), shs[0], shs[1]);   // the direction is constant along the ray: SH once per tile,
             if (leader) {                                                       // kept in this lane's shared-memory slot
                 const float4 r0 = __ldcg(state_in + 2 * (size_t)index), r1 = __ldcg(state_in + 2 * (size_t)index + 1);
                 rs[0] = make_float4(r0.x, r0.y, r0.z, r1.w);
@@ -1080,9 +1087,17 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
 
     // ---- prologue: near/far, ray state, first live list (renderer.py:273-274, 335-343)
     for (uint32_t n = blockIdx.x * blockDim.x + tid; n < N; n += gridDim.x * blockDim.x) {
-        const float *o = ra.rays_o + (size_t)n * 3, *d = ra.rays_d + (size_t)n * 3;
+        float o[3], d[3];
+        if (ra.poses) {
+            pose_ray(ra.poses + (size_t)(n / ra.img_hw) * 16, n % ra.img_hw, ra.img_w, ra.fx, ra.fy, ra.cx, ra.cy, o, d);
+#pragma unroll
+            for (int k = 0; k < 3; k++) { ra.gen_o[(size_t)n * 3 + k] = o[k]; ra.gen_d[(size_t)n * 3 + k] = d[k]; }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; k++) { o[k] = __ldg(ra.rays_o + (size_t)n * 3 + k); d[k] = __ldg(ra.rays_d + (size_t)n * 3 + k); }
+        }
         float near, far;
-        if (!slab_near_far(__ldg(o), __ldg(o + 1), __ldg(o + 2), __ldg(d), __ldg(d + 1), __ldg(d + 2), ra.aabb, ra.min_near, near, far))
+        if (!slab_near_far(o[0], o[1], o[2], d[0], d[1], d[2], ra.aabb, ra.min_near, near, far))
             near = far = FLT_MAX;
         ra.nears[n] = near; ra.fars[n] = far;
         ra.alive[0][n] = (int)n;
@@ -1571,6 +1586,10 @@ struct RenderExtras {   // ngp_render_uq's optional outputs
     uint32_t dump_rows = 0;
     int32_t *ray_info = nullptr;
     int64_t *dump_header = nullptr;
+    // rays from poses: rays_o / rays_d passed to render_core are then OUTPUT buffers the prologue fills
+    const float *poses = nullptr;
+    uint32_t img_h = 0, img_w = 0;
+    float fx = 0, fy = 0, cx = 0, cy = 0;
 };
 static int render_core(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps, float bg_color,
                        float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, const RenderExtras &ex, void *stream);
@@ -1628,7 +1647,9 @@ static int render_core(ngp_ctx *c, const float *rays_o, const float *rays_d, uin
 #endif
     NGP_CUDA(cudaMemsetAsync(c->ctr, 0, sizeof(RenderCtr), st));
     RenderArgs ra{};
-    ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps;
+    ra.rays_o = rays_o; ra.rays_d = rays_d; ra.N = N;
+    ra.poses = ex.poses; ra.gen_o = ex.poses ? const_cast<float *>(rays_o) : nullptr; ra.gen_d = ex.poses ? const_cast<float *>(rays_d) : nullptr;
+    ra.img_w = ex.img_w; ra.img_hw = ex.img_h * ex.img_w; ra.fx = ex.fx; ra.fy = ex.fy; ra.cx = ex.cx; ra.cy = ex.cy; ra.min_near = c->min_near; ra.bg_color = bg_color; ra.max_steps = max_steps;
     for (int i = 0; i < 6; i++) ra.aabb[i] = c->aabb[i];
     ra.mc = make_march_const(c->nc.bound, dt_gamma, max_steps, c->cascade, c->grid_size, c->bitfield);
     ra.nears = c->nears; ra.fars = c->fars; ra.state[0] = c->state[0]; ra.state[1] = c->state[1]; ra.n_emit = c->n_emit;
@@ -1727,8 +1748,10 @@ int ngp_render_poses_host(ngp_ctx *c, const float *poses_host, uint32_t F, uint3
     if (int rc = ensure_host_staging(c, N, F)) return rc;
     cudaStream_t st = as_stream(stream);
     NGP_CUDA(cudaMemcpyAsync(c->d_poses, poses_host, sizeof(float) * 16 * (size_t)F, cudaMemcpyHostToDevice, st));   // 64 B per frame
-    if (int rc = ngp_get_rays(c->d_poses, F, H, W, fx, fy, cx, cy, c->d_o, c->d_d, stream)) return rc;
-    if (int rc = ngp_render(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, c->d_img, c->d_depth, c->d_ws, nullptr, nullptr, stream)) return rc;
+    NGP_REQUIRE(fx != 0.f && fy != 0.f, "render_poses_host: zero focal length");
+    RenderExtras ex;   // the renderer's prologue generates the rays (nerf/utils.py:52-116) into the staging buffers itself
+    ex.poses = c->d_poses; ex.img_h = H; ex.img_w = W; ex.fx = fx; ex.fy = fy; ex.cx = cx; ex.cy = cy;
+    if (int rc = render_core(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, c->d_img, c->d_depth, c->d_ws, nullptr, nullptr, ex, stream)) return rc;
     return finish_host_render(c, N, image_host, depth_host, st, "render_poses_host");
 }
 

@@ -33,18 +33,10 @@ __global__ void __launch_bounds__(kThreads) k_get_rays(const float *__restrict__
     const uint32_t HW = H * W;
     if (n >= (size_t)F * HW) return;
     const uint32_t f = (uint32_t)(n / HW), p = (uint32_t)(n % HW);
-    const float *P = poses + (size_t)f * 16;
-    const float i = __fadd_rn((float)(p % W), 0.5f), j = __fadd_rn((float)(p / W), 0.5f);
-    const float x = __fdiv_rn(__fsub_rn(i, cx), fx), y = __fdiv_rn(__fsub_rn(j, cy), fy);
-    const float nrm = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), 1.0f));
-    const float d0 = __fdiv_rn(x, nrm), d1 = __fdiv_rn(y, nrm), d2 = __fdiv_rn(1.0f, nrm);
-    float *o = rays_o + n * 3, *d = rays_d + n * 3;
+    float o[3], d[3];
+    pose_ray(poses + (size_t)f * 16, p, W, fx, fy, cx, cy, o, d);
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-        const float r0 = __ldg(P + 4 * k), r1 = __ldg(P + 4 * k + 1), r2 = __ldg(P + 4 * k + 2);
-        d[k] = __fadd_rn(__fadd_rn(__fmul_rn(d0, r0), __fmul_rn(d1, r1)), __fmul_rn(d2, r2));
-        o[k] = __ldg(P + 4 * k + 3);
-    }
+    for (int k = 0; k < 3; k++) { rays_o[n * 3 + k] = o[k]; rays_d[n * 3 + k] = d[k]; }
 }
 
 // raymarching/src/raymarching.cu:216-262

@@ -16,8 +16,9 @@ __all__ = ["near_far_from_aabb", "sph_from_ray", "morton3D", "morton3D_invert", 
 
 
 def _f32c(t):
-    if not t.is_cuda:
-        t = t.cuda()  # raymarching.py:34-35 does the same
+    # the reference moves CPU tensors to the GPU silently (raymarching.py:34-35); here a CPU tensor is an error, as include/ngp_b200.h
+    # and DESIGN.md say: there is no CPU path, and a hidden host-to-device copy per call is not one either
+    _cabi.require_cuda(t)
     return t.float().contiguous()
 
 
@@ -42,8 +43,7 @@ def sph_from_ray(rays_o, rays_d, radius):
 def morton3D(coords):
     """raymarching.py:83-104: coords int32 [N,3] in [0,1024) -> indices int32 [N]."""
     lib = _cabi.load()
-    if not coords.is_cuda:
-        coords = coords.cuda()
+    _cabi.require_cuda(coords)
     coords = coords.int().contiguous()
     N = coords.shape[0]
     indices = torch.empty(N, dtype=torch.int32, device=coords.device)
@@ -54,8 +54,7 @@ def morton3D(coords):
 def morton3D_invert(indices):
     """raymarching.py:106-126: indices int32 [N] -> coords int32 [N,3]."""
     lib = _cabi.load()
-    if not indices.is_cuda:
-        indices = indices.cuda()
+    _cabi.require_cuda(indices)
     indices = indices.int().contiguous()
     N = indices.shape[0]
     coords = torch.empty(N, 3, dtype=torch.int32, device=indices.device)

@@ -70,7 +70,7 @@ def build(name: str) -> str:
 # The reference's own Python on the path, unmodified, so that the GPU box (which has no /root/reference) can run its methods on the
 # rebuilt extensions: tests/refext.reference_renderer_class() imports nerf/renderer.py from here behind three stub modules.  Like the
 # .so files these are build OUTPUTS: oracle/_ref/ is git-ignored, nothing of it enters the repository's history.
-PYREF = ["nerf/renderer.py"]
+PYREF = ["nerf/renderer.py", "nerf/network_ff.py", "validate.py"]
 
 
 def copy_python():

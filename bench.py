@@ -14,9 +14,10 @@ weights, no data-path collective) => weak scaling; `value` = rays of all ranks /
 `e2e`      the same frame through ngp_render_host: pinned host rays -> H2D -> render -> D2H image+depth, inside the timer.
 `roofline` dominant kernel = k_render (99.9 % of a step, profiles/): algorithmic 512 B gathered per sample (16 levels x 8
            corners x 2 ch x 2 B) x samples counted by the kernel, over the measured HBM copy peak
-           (MEASURED_PEAKS.json).  The 2^19 table (23.3 MB fp16) is L2-resident on B200 and every 4-byte corner costs a whole
-           32-byte sector / one L1 wavefront, so the binding roof is the measured random-gather rate (tools/gather_peak.cu,
-           profiles/r01_gather_peak.jsonl: 289 G gathers/s at 16 MB), reported beside it as `roofline.gather`.
+           (MEASURED_PEAKS.json).  `traffic` = DRAM bytes of one launch from the committed ncu capture of THIS build and workload
+           (profiles/r02_ncu_metrics.json).  The 2^19 table (23.3 MB fp16) is L2-resident on B200, so beside the HBM figure the
+           line carries the roof that fits the access pattern -- `l1_wavefront`: ncu-counted L1 wavefronts of the gather at one
+           per cycle per SM -- and the tensor-pipe fraction.
 `cpu_baseline`  oracle/ngp_oracle.c (OpenMP port of the reference path) on a strided sub-sample of the same frame.
 `--impl reference`  the same CPU port on all host threads, as the reference arm (the reference has no CPU
            implementation of the NGP path; its CUDA extensions rebuilt for sm_100a are timed beside it as `reference_gpu`).
@@ -47,20 +48,16 @@ WORKLOADS = {
 }
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch from the committed `ncu --set full` capture
-# (profiles/r01*_k_render_ncu_summary.txt); None where no capture exists
-NCU_DRAM_BYTES_PER_LAUNCH = {"cfg2": 2834868000}   # profiles/r01n_k_render_ncu_summary.txt: 1.396 GB read + 1.439 GB written (the epoch sample buffer spills past L2)
+# The build the committed ncu metrics (profiles/r02_ncu_metrics.json, made by tools/ncu_metrics_json.py from `ncu --set full` captures of
+# k_render on this workload) belong to.  Bump it together with the file; a mismatch reports `traffic: null` instead of a stale number.
+PROFILE_BUILD = "r02h"
 
 
-def measured_gather_peak():
-    """G gathers/s of random 4-byte loads from a 16 MB (L2-resident) table, measured by tools/gather_peak.cu."""
+def ncu_metrics(workload):
+    """{dram_bytes, l1_global_load_wavefronts, ...} of one k_render launch of `workload`, or None when no capture of this build exists."""
     try:
-        best = 0.0
-        for ln in open(os.path.join(ROOT, "profiles", "r01_gather_peak.jsonl")):
-            d = json.loads(ln)
-            if d["test"] == "random4" and d["table_mb"] == 16.0:
-                best = max(best, d["ggathers_per_s"])
-        return best or None
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")))
+        return d.get(workload) if d.get("build") == PROFILE_BUILD else None
     except Exception:
         return None
 
@@ -375,8 +372,24 @@ def main():
         value = rays_all / (ms_step * 1e-3) / 1e6
         e2e_value = rays_all / (ms_e2e / args.steps * 1e-3) / 1e6
         achieved = samples * 512 / (ms_step * 1e-3) / 1e9    # this rank's kernel: its own samples / its own launch time
-        gather_peak = measured_gather_peak()
-        ggathers = samples * 128 / (ms_step * 1e-3) / 1e9
+        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        ncu = None if args.variant != "A" and args.workload == "cfg2" else ncu_metrics(args.workload)
+        tensor_peak = float(peaks.get("bf16_tflops_sustained", 1363.0))
+        tensor_ach = samples * 36864 / (ms_step * 1e-3) / 1e12
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                    "traffic": int(ncu["dram_bytes"]) if ncu else None, "kernel": "k_render", "algorithmic_bytes_per_sample": 512,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                    # The table is served from L2 / L1 (traffic above = what reaches DRAM), so the roof that fits this access pattern is
+                    # the L1 data pipe: one wavefront per cycle per SM.  The wavefront count is ncu's, of this build on this workload
+                    # (K consecutive samples of a ray sit in adjacent lanes, so coarse levels coalesce); floor = wavefronts / (SMs x clock).
+                    "l1_wavefront": ({"wavefronts_per_launch": int(ncu["l1_global_load_wavefronts"]),
+                                      "floor_ms": ncu["l1_global_load_wavefronts"] / n_sm / (sm_max * 1e3),
+                                      "frac": ncu["l1_global_load_wavefronts"] / n_sm / (sm_max * 1e3) / ms_step,
+                                      "source": f"profiles/r02_ncu_metrics.json (build {PROFILE_BUILD}, {ncu['report']})"} if ncu else None),
+                    "tensor": {"achieved_tflops": tensor_ach, "peak_tflops": tensor_peak, "frac": tensor_ach / tensor_peak,
+                               "what": "36864 algorithmic FLOP per sample (7 layers, 64-wide) over bf16_tflops_sustained; the kernel issues "
+                                       "every layer once per 32-row lane quadrant (masked M=128 MMAs), 4x that on the pipe"}}
         line = {"metric": "rendered Mrays/s (NGP hashgrid, cuda_ray inference)", "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if split_rows else "weak",
                 "vs_baseline": None, "dtype": "f16 storage / f32 accumulate", "data": "synthetic",
@@ -391,16 +404,9 @@ def main():
                 "e2e_from_pose": None if not ms_pose else {
                     "value": rays_all / (ms_pose / args.steps * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(pose_pin.numel() * 4),
                     "d2h_bytes_per_step": int(img_pin.numel() * 4 + dep_pin.numel() * 4), "ms_per_step": ms_pose / args.steps,
-                    "api": "ngp_render_poses_host (C ABI: host 4x4 pose in, rays generated on the device by ngp_get_rays, host image + depth out)"},
+                    "api": "ngp_render_poses_host (C ABI: host 4x4 pose in, rays generated in the render kernel's prologue, host image + depth out)"},
                 "gpu_launches": int(launches),
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                             "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload), "kernel": "k_render", "algorithmic_bytes_per_sample": 512,
-                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
-                             "gather": {"achieved_ggathers_per_s": ggathers, "peak_ggathers_per_s": gather_peak,
-                                        "frac": ggathers / gather_peak if gather_peak else None,
-                                        "peak_source": "tools/gather_peak.cu on this pool's B200 (profiles/r01_gather_peak.jsonl): random 4 B "
-                                                       "gathers from a 16 MB L2-resident table"},
-                             "tensor_tflops_achieved": samples * 36864 / (ms_step * 1e-3) / 1e12},
+                "roofline": roofline,
                 "clocks": clocks.summary()}
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1

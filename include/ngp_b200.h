@@ -187,6 +187,12 @@ int ngp_render_host(ngp_ctx *ctx, const float *rays_o_host, const float *rays_d_
                     float dt_gamma, uint32_t max_steps, float bg_color, float *image_host, float *depth_host,
                     void *stream);
 
+/* ngp_render for F camera frames given as cam2world poses [F,4,4] fp32 (DEVICE): the rays of every pixel (nerf/utils.py:52-116, N = -1)
+ * are generated in the render kernel's prologue -- no ray tensors cross the boundary (64 B per frame instead of 24 B per ray).
+ * Outputs as ngp_render with N = F * H * W rays in frame-major, row-major pixel order. */
+int ngp_render_poses(ngp_ctx *ctx, const float *poses, uint32_t F, uint32_t H, uint32_t W, float fx, float fy,
+                     float cx, float cy, float dt_gamma, uint32_t max_steps, float bg_color, float *image,
+                     float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats, void *stream);
 /* Estimator.render_from_pose (nav/estimator_helpers.py:236-243) for a batch of F cameras: HOST poses [F,4,4] in (64 B per
  * frame instead of 24 B per ray), rays generated on the device (ngp_get_rays), one render over all F*H*W rays (one n_step
  * schedule, exactly like renderer.py:265-269 flattens a [F,N,3] batch), HOST image [F*H*W,3] / depth [F*H*W] out; synchronous. */

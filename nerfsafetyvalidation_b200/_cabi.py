@@ -46,6 +46,7 @@ _SIGNATURES = {
     "ngp_render_uq": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p, _p, _u64, _p, _p, _p],
     "ngp_render_sample_rows": [_p, _u32, C.POINTER(_u64)],
     "ngp_render_host": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p],
+    "ngp_render_poses": [_p, _p, _u32, _u32, _u32, _f32, _f32, _f32, _f32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render_poses_host": [_p, _p, _u32, _u32, _u32, _f32, _f32, _f32, _f32, _f32, _u32, _f32, _p, _p, _p],
 }
 _RESTYPES = {"ngp_last_error": C.c_char_p, "ngp_launch_count": _u64, "ngp_compact_scratch_bytes": _u64}

@@ -1737,6 +1737,22 @@ int ngp_render_host(ngp_ctx *c, const float *rays_o_host, const float *rays_d_ho
     return finish_host_render(c, N, image_host, depth_host, st, "render_host");
 }
 
+int ngp_render_poses(ngp_ctx *c, const float *poses, uint32_t F, uint32_t H, uint32_t W, float fx, float fy, float cx, float cy, float dt_gamma,
+                     uint32_t max_steps, float bg_color, float *image, float *depth, float *weights_sum, int32_t *samples_per_ray, int64_t *stats,
+                     void *stream) {
+    NGP_REQUIRE(c != nullptr, "render_poses: null ctx");
+    const unsigned long long n = (unsigned long long)F * H * W;
+    if (n == 0) return 0;
+    NGP_REQUIRE(n <= 0xffffffffull, "render_poses: %llu rays exceed the 32-bit ray index of the renderer", n);
+    NGP_REQUIRE(fx != 0.f && fy != 0.f, "render_poses: zero focal length");
+    NGP_DEVPTR(poses);
+    const uint32_t N = (uint32_t)n;
+    if (int rc = ensure_host_staging(c, N, 0)) return rc;   // d_o / d_d: where the prologue leaves the rays for the later phases
+    RenderExtras ex;
+    ex.poses = poses; ex.img_h = H; ex.img_w = W; ex.fx = fx; ex.fy = fy; ex.cx = cx; ex.cy = cy;
+    return render_core(c, c->d_o, c->d_d, N, dt_gamma, max_steps, bg_color, image, depth, weights_sum, samples_per_ray, stats, ex, stream);
+}
+
 int ngp_render_poses_host(ngp_ctx *c, const float *poses_host, uint32_t F, uint32_t H, uint32_t W, float fx, float fy, float cx, float cy,
                           float dt_gamma, uint32_t max_steps, float bg_color, float *image_host, float *depth_host, void *stream) {
     NGP_REQUIRE(c != nullptr, "render_poses_host: null ctx");

@@ -297,7 +297,8 @@ __device__ __forceinline__ void layer_ts(Tile &t, int lane, uint32_t a_col, uint
     tmem_st_wait();          // this warp's A-row stores have landed in tensor memory
     fence_before_sync();     // ... and are ordered, with its tcgen05.ld of the previous accumulators, before the hand-over to lane 0
     __syncwarp();
-    if (lane == 0) {
+    (void)lane;
+    if (elect_one()) {
         fence_after_sync();
         const uint32_t base = t.tmem & 0x0000FFFFu;   // lane 0 of the tile
         issue_layer_ts_quadrant(base + kColD, base + a_col, t.w_saddr + w_off, N, K, t.q);

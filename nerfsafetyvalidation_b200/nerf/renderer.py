@@ -368,13 +368,39 @@ class NeRFRenderer(nn.Module):
         return {"depth": depth, "image": image, "rgbs": part["rgbs"], "sigmas": part["sigmas"], "aggregated_density": aggregated_density}
 
     @torch.no_grad()
-    def render_poses(self, poses, intrinsics, H, W, **kwargs):
+    def render_poses(self, poses, intrinsics, H, W, dt_gamma=0, bg_color=1, max_steps=1024, perturb=False, return_stats=False, **kwargs):
         """Estimator.render_from_pose (nav/estimator_helpers.py:236-243) for a batch: poses [F,4,4] cam2world (CUDA, NGP frame),
-        intrinsics (fx, fy, cx, cy) -> render() result with image [F, H*W, 3], depth [F, H*W].  Rays are generated on the device
-        by ngp_get_rays (nerf/utils.py:52-116)."""
+        intrinsics (fx, fy, cx, cy) -> render() result with image [F, H*W, 3], depth [F, H*W].  On the fused path the rays
+        (nerf/utils.py:52-116) are generated inside the render kernel (ngp_render_poses); otherwise by ngp_get_rays + render()."""
+        scalar_bg = not torch.is_tensor(bg_color)
+        if (self.cuda_ray and self.fused and not self.training and self.bg_radius <= 0 and not perturb and scalar_bg and not kwargs.get("return_uq")
+                and kwargs.get("fused", True) and self._configure_native(self._native)):
+            _cabi.require_cuda(poses)
+            poses = poses.detach().to(torch.float32).contiguous()
+            if tuple(poses.shape[1:]) != (4, 4):
+                raise RuntimeError(f"render_poses: poses must be [F,4,4], got {tuple(poses.shape)}")
+            F, device = poses.shape[0], poses.device
+            N = F * H * W
+            image = torch.empty(N, 3, dtype=torch.float32, device=device)
+            depth = torch.empty(N, dtype=torch.float32, device=device)
+            weights_sum = torch.empty(N, dtype=torch.float32, device=device)
+            spr = torch.empty(N, dtype=torch.int32, device=device) if return_stats else None
+            stats = torch.zeros(4, dtype=torch.int64, device=device) if return_stats else None
+            fx, fy, cx, cy = (float(v) for v in intrinsics)
+            with torch.cuda.device(device):
+                handle = self._native.get(device)
+                self._set_scene(self._native, handle)
+                _cabi.check(_cabi.load().ngp_render_poses(handle, _cabi.ptr(poses), F, H, W, fx, fy, cx, cy, float(dt_gamma), int(max_steps),
+                                                          float(bg_color), _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum),
+                                                          _cabi.ptr(spr), _cabi.ptr(stats), _cabi.stream()), "ngp_render_poses")
+            out = {"depth": depth.view(F, H * W), "image": image.view(F, H * W, 3), "weights_sum": weights_sum, "sigmas": None, "rgbs": None}
+            if return_stats:
+                out["samples_per_ray"], out["stats"] = spr, stats
+            return out
         from .utils import get_rays
         r = get_rays(poses, intrinsics, H, W)
-        return self.render(r["rays_o"], r["rays_d"], **kwargs)
+        return self.render(r["rays_o"], r["rays_d"], dt_gamma=dt_gamma, bg_color=bg_color, max_steps=max_steps, perturb=perturb,
+                           return_stats=return_stats, **kwargs)
 
     @torch.no_grad()
     def render_poses_host(self, poses, intrinsics, H, W, image=None, depth=None, dt_gamma=0, bg_color=1, max_steps=1024):

@@ -14,6 +14,7 @@ What validate.py's stress tests do around the hot path, reduced to what feeds an
 Host-side logic only (numpy + torch.distributed for the two small collectives; `gloo` on CPU in the tests, `nccl` on GPUs).
 The Blender image fetch, SIFT estimator, planner and UQ of the real simulator step are out of scope (graphics / CPU control code).
 """
+import contextlib
 import math
 
 import numpy as np
@@ -252,11 +253,13 @@ def render_rollouts(model, ids, steps, H, W, focal, frames_per_call=64, mean=Non
     poses = torch.from_numpy(states_to_ngp_poses(rollout_states(noise).reshape(-1, 12))).to(dev)
     risks = []
     centre = (H // 2) * W + W // 2
-    with torch.no_grad():
+    intr = (focal, focal, W / 2, H / 2)
+    frozen = model.frozen_weights() if hasattr(model, "frozen_weights") else contextlib.nullcontext()
+    with torch.no_grad(), frozen:
         for f0 in range(0, poses.shape[0], frames_per_call):
-            o, d = get_rays_device(poses[f0:f0 + frames_per_call], focal, focal, W / 2, H / 2, H, W)
-            out = model.render(o, d, bg_color=1, perturb=False, **render_kw)
-            F = o.shape[0]
+            # 64 B per frame in: the rays (get_rays, nerf/utils.py:52-116) are generated inside the render kernel
+            out = model.render_poses(poses[f0:f0 + frames_per_call], intr, H, W, bg_color=1, perturb=False, **render_kw)
+            F = out["depth"].shape[0]
             # per-frame clearance along the optical axis: normalised depth of what the centre ray hit, pushed to 1 where it
             # hit nothing (weights_sum ~ 0); missed rays have NaN depth (renderer.py:376)
             dc = torch.nan_to_num(out["depth"][:, centre], nan=1.0)

@@ -91,20 +91,19 @@ __device__ __forceinline__ void encode_trip(const NetConst &nc, float u0, float 
 #pragma unroll
         for (int k = 0; k < 8; k++) v[j][k] = __ldg(tl + row[k]);
     }
-#ifndef NGP_FP32_BLEND   // default: trilinear blend in packed fp16 (HMUL2 / HFMA2, weights and sum rounded to half like the reference's own
-                        // accumulator, gridencoder.cu:146-171) instead of fp32 FFMA2 after 16 conversions per level: -2 % frame time, and
-                        // the image's distance from the reference extensions is unchanged (1.4e-4, set by the fp32- vs fp16-accumulated MLPs)
+#ifndef NGP_FP32_BLEND   // default: trilinear blend in packed fp16 (both channels of a corner in one HFMA2; intermediate results rounded
+                        // to half like the reference's own accumulator, gridencoder.cu:146-171) instead of fp32 FFMA2 after 16
+                        // conversions per level: -2 % frame time, and the image's distance from the reference extensions is unchanged
+                        // (1.4e-4, set by the fp32- vs fp16-accumulated MLPs).  Written as the lerp tree x -> y -> z (14 packed
+                        // operations per level, no per-corner weight products or broadcasts).
 #pragma unroll
     for (int j = 0; j < LPT; j++) {
-        const float p0 = f[j][0], p1 = f[j][1], p2 = f[j][2];
-        const __half2 wx = __floats2half2_rn(1.0f - p0, p0);
-        const __half2 hq1 = __float2half2_rn(1.0f - p1), hp1 = __float2half2_rn(p1), hq2 = __float2half2_rn(1.0f - p2), hp2 = __float2half2_rn(p2);
-        const __half2 w0 = __hmul2(wx, hq1), w1 = __hmul2(wx, hp1);
-        const __half2 w[4] = {__hmul2(w0, hq2), __hmul2(w1, hq2), __hmul2(w0, hp2), __hmul2(w1, hp2)};   // corner pairs (0,1) (2,3) (4,5) (6,7)
-        __half2 acc = __float2half2_rn(0.f);
-#pragma unroll
-        for (int k = 0; k < 8; k++) acc = __hfma2((k & 1) ? __high2half2(w[k >> 1]) : __low2half2(w[k >> 1]), v[j][k], acc);
-        packed[j] = *reinterpret_cast<const uint32_t *>(&acc);
+        const __half2 fx = __float2half2_rn(f[j][0]), fy = __float2half2_rn(f[j][1]), fz = __float2half2_rn(f[j][2]);
+        const __half2 a0 = __hfma2(fx, __hsub2(v[j][1], v[j][0]), v[j][0]), a1 = __hfma2(fx, __hsub2(v[j][3], v[j][2]), v[j][2]);
+        const __half2 a2 = __hfma2(fx, __hsub2(v[j][5], v[j][4]), v[j][4]), a3 = __hfma2(fx, __hsub2(v[j][7], v[j][6]), v[j][6]);
+        const __half2 b0 = __hfma2(fy, __hsub2(a1, a0), a0), b1 = __hfma2(fy, __hsub2(a3, a2), a2);
+        const __half2 c = __hfma2(fz, __hsub2(b1, b0), b0);
+        packed[j] = *reinterpret_cast<const uint32_t *>(&c);
     }
     return;
 #endif
@@ -473,7 +472,10 @@ constexpr int kMaxEpoch = 128;                 // reference iterations per epoch
 constexpr int kMaxSamplesPerEpoch = NGP_MAX_SAMPLES_PER_EPOCH;      // E * s cap: bounds the longest tile of an epoch
 constexpr int kScratchPerWarp = 32 * (2 + 3 + 2);   // float4 per epilogue warp: compositing scratch (2 per lane) + ray state (3) + SH row (2)
 constexpr uint32_t kTilesPerTicket = 1;      // EVALUATE: consecutive 32-row warp tiles (adjacent rays: shared hash-grid cells) per claimed ticket
-constexpr int kRefillLanes = 8;                // a warp refills its idle lanes from the live list once this many are idle
+#ifndef NGP_REFILL_LANES
+#define NGP_REFILL_LANES 8
+#endif
+constexpr int kRefillLanes = NGP_REFILL_LANES;                // a warp refills its idle lanes from the live list once this many are idle
 
 struct EpochCtr {
     uint32_t cursor;            // MARCH phase: next unclaimed entry of the live list

@@ -1,18 +1,18 @@
 // tc_mlp.cuh -- the fully fused 64-wide density + colour MLP on Blackwell's 5th-generation tensor cores (tcgen05).
 //
-// Replaces, for the fused paths, the mma.sync formulation of ffmlp/src/ffmlp.cu:331-407 (kernel_mlp_fused, wmma 16x16x16):
-//   * one 128-row tile per WARPGROUP (4 warps; thread = row = TMEM lane), D accumulators (128 x 64 fp32) in tensor memory;
-//   * every layer is `tcgen05.mma.cta_group::1.kind::f16` M=128, N=64|16, K=16 issued by ONE thread, A (activations) and B (weights)
-//     read straight from shared memory through matrix descriptors;
-//   * between layers each thread pulls its own row back with `tcgen05.ld.32x32b`, applies ReLU + fp16 rounding in registers and
-//     stores the row as the next layer's A operand.  No accumulator, A fragment or B fragment ever lives in the register file
-//     across the tile, which is what lets the renderer keep twice as many warps resident as the mma.sync version.
+// Replaces, for the fused paths, the wmma formulation of ffmlp/src/ffmlp.cu:331-407 (kernel_mlp_fused, 16x16x16 fragments):
+//   * a tile is 128 sample rows = the 128 TMEM lanes; thread = row; a warp owns the 32 rows of its lane quadrant (warp % 4);
+//   * every layer is `tcgen05.mma.cta_group::1.kind::f16` M=128, N=64|16, K=16 per instruction, issued by ONE elected thread:
+//     A (activations) is read from TENSOR MEMORY (fp16, two halves per 32-bit column, row = lane: what tcgen05.st.32x32b writes),
+//     B (weights) from shared memory through a matrix descriptor, D (fp32 accumulators) lives in tensor memory;
+//   * with an output-lane mask a warp runs the layer for ITS 32 rows only, so the four quadrants of a tile are independent chains:
+//     tcgen05.ld D -> ReLU / fp16 -> tcgen05.st next A -> issue next layer -> wait for its commit, no other warp involved;
+//   * no accumulator, A fragment or B fragment ever lives in the register file across a layer, and no activation in shared memory.
 //
-// Shared-memory operand layout (both A and B), K-major, no swizzle:  uint4 tile[K / 8][rows]
-//     element (row r, k) lives in tile[k / 8][r], half k % 8.  In the descriptor's terms (cute/arch/mma_sm100_desc.hpp,
-//     "Major-K, INTERLEAVE: ((8,n),2):((1,SBO),LBO)" in 16-byte units): 8 consecutive rows of one 16-byte K-chunk are the 128-byte
-//     core matrix, SBO = 128 B between 8-row groups, LBO = rows * 16 B between K-chunks.  A row-per-thread store of one chunk is
-//     32 consecutive uint4 per warp: conflict-free.
+// Shared-memory layout of a weight matrix [N x K] (K-major, no swizzle):  uint4 w[K / 8][N]
+//     element (n, k) lives in w[k / 8][n], half k % 8.  In the descriptor's terms (cute/arch/mma_sm100_desc.hpp, "Major-K,
+//     INTERLEAVE: ((8,n),2):((1,SBO),LBO)" in 16-byte units): 8 consecutive rows of one 16-byte K-chunk are the 128-byte core
+//     matrix, SBO = 128 B between 8-row groups, LBO = N * 16 B between K-chunks.
 #pragma once
 #include <cuda_fp16.h>
 #include <stdint.h>

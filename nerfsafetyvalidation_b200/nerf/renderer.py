@@ -4,7 +4,8 @@
 signatures and result dict (nerf/renderer.py:261-386, 549-588).  Two execution modes for the inference branch:
 
   fused (default)   the whole loop of renderer.py:329-376 is ONE persistent cooperative kernel (ngp_render):
-                    near/far -> {march -> hash-grid -> MLPs -> composite -> stable compaction} with the reference's
+                    near/far -> {march -> hash-grid -> MLPs -> composite -> compaction (survivors appended unordered;
+                    per-ray results do not depend on the order)} with the reference's
                     global `n_step = clamp(N // n_alive, 1, 8)` schedule evaluated on the device, then background
                     mix and depth normalisation.  No host sync, no intermediate tensors in HBM.
   stepwise          the reference's Python loop verbatim, on our stand-alone ops (one launch per op per

@@ -87,6 +87,15 @@ int ngp_composite_rays(uint32_t n_alive, uint32_t n_step, int32_t *rays_alive, f
 uint64_t ngp_compact_scratch_bytes(uint32_t n);
 int ngp_compact_alive(const int32_t *in, uint32_t n, int32_t *out, uint32_t *d_count, void *d_scratch,
                       void *stream);
+/* No counterpart in the reference; added for callers that cannot
+ * allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
+ * ngp_compact_alive, but the look-back scratch is a file-scope __device__ array of the library (about 16 KiB,
+ * held by every GPU that loads the library until exit), so the call allocates nothing.  n above
+ * NGP_COMPACT_STATIC_MAX_N is rejected with an error.  All calls on one device share the array: the call
+ * clears what it reads on `stream` first, and two calls that overlap on the GPU (different streams without
+ * an ordering between them) race -- serialise them or use ngp_compact_alive with separate scratch. */
+#define NGP_COMPACT_STATIC_MAX_N (1u << 22)
+int ngp_compact_alive_static(const int32_t *in, uint32_t n, int32_t *out, uint32_t *d_count, void *stream);
 
 /* ---------------------------------------------------------------- encoders
  * replaces _gridencoder.grid_encode_forward (gridencoder/src/bindings.cpp:5-8, gridencoder.cu:423-446)

@@ -28,6 +28,7 @@ _SIGNATURES = {
     "ngp_composite_rays": [_u32, _u32, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "ngp_compact_scratch_bytes": [_u32],
     "ngp_compact_alive": [_p, _u32, _p, _p, _p, _p],
+    "ngp_compact_alive_static": [_p, _u32, _p, _p, _p],
     "ngp_grid_encode_forward": [_p, _p, _i32, _p, _p, _u32, _u32, _u32, _u32, _f32, _u32, _u32, _i32, _i32, _i32, _p, _p],
     "ngp_grid_level_scales": [_u32, _f32, _u32, _p, _p],
     "ngp_sh_encode_forward": [_p, _p, _u32, _u32, _p],

@@ -2,6 +2,7 @@
 // _raymarching extension, inference + setup functions) and the sync-free stable compaction that replaces
 // `rays_alive[rays_alive >= 0]` (nerf/renderer.py:369).
 #include <float.h>
+#include <mutex>
 
 #include "common.cuh"
 #include "device_math.cuh"
@@ -163,6 +164,33 @@ __global__ void __launch_bounds__(kCpThreads) k_compact(const int *__restrict__ 
         if (v[k] >= 0) out[pos++] = v[k];
 }
 
+// Scratch of ngp_compact_alive_static: ticket word + look-back status words for at most kCompactStaticMaxN
+// elements, resident in every device that loads the library.  In host code this name is only a handle for
+// cudaGetSymbolAddress; the kernel gets the per-device address resolved below.
+constexpr uint32_t kCompactStaticMaxN = 1u << 22;
+constexpr size_t kCompactStaticBytes = 16 + 8 * (size_t)(kCompactStaticMaxN / kCpTile + 1);
+static __device__ __align__(256) unsigned char g_compact_scratch[(kCompactStaticBytes + 255) / 256 * 256];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_compact_scratch_mu;
+static void *g_compact_scratch_addr[kMaxDevices] = {};
+
+// Device address of g_compact_scratch on the CURRENT device, resolved once per device.
+static int compact_static_scratch(void **addr) {
+    int dev = -1;
+    NGP_CUDA(cudaGetDevice(&dev));
+    NGP_REQUIRE(dev >= 0 && dev < kMaxDevices, "compact_alive_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    std::lock_guard<std::mutex> lock(g_compact_scratch_mu);
+    if (!g_compact_scratch_addr[dev]) {
+        void *p = nullptr;
+        NGP_CUDA(cudaGetSymbolAddress(&p, g_compact_scratch));
+        NGP_REQUIRE(p != nullptr, "compact_alive_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+        g_compact_scratch_addr[dev] = p;
+    }
+    *addr = g_compact_scratch_addr[dev];
+    return 0;
+}
+
 }  // namespace ngp
 
 using namespace ngp;
@@ -255,6 +283,28 @@ int ngp_compact_alive(const int32_t *in, uint32_t n, int32_t *out, uint32_t *d_c
     unsigned long long *status = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(d_scratch) + 16);
     k_compact<<<n_tiles, kCpThreads, 0, as_stream(stream)>>>(in, n, out, d_count, ticket, status, n_tiles);
     return after_launch("compact_alive");
+}
+
+int ngp_compact_alive_static(const int32_t *in, uint32_t n, int32_t *out, uint32_t *d_count, void *stream) {
+    NGP_DEVPTR(d_count);
+    NGP_REQUIRE(n <= kCompactStaticMaxN,
+                "compact_alive_static: n = %u exceeds the built-in scratch (at most %u elements); use ngp_compact_alive with caller scratch",
+                n, kCompactStaticMaxN);
+    if (n == 0) {
+        NGP_CUDA(cudaMemsetAsync(d_count, 0, sizeof(uint32_t), as_stream(stream)));
+        return 0;
+    }
+    NGP_DEVPTR(in); NGP_DEVPTR(out);
+    NGP_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0, "compact_alive_static: `in` must be 16-byte aligned");
+    void *scratch = nullptr;
+    if (int rc = compact_static_scratch(&scratch)) return rc;
+    const uint32_t n_tiles = div_up(n, kCpTile);
+    // the array keeps the previous call's ticket and status words: clear the part this call reads
+    NGP_CUDA(cudaMemsetAsync(scratch, 0, ngp_compact_scratch_bytes(n), as_stream(stream)));
+    uint32_t *ticket = reinterpret_cast<uint32_t *>(scratch);
+    unsigned long long *status = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(scratch) + 16);
+    k_compact<<<n_tiles, kCpThreads, 0, as_stream(stream)>>>(in, n, out, d_count, ticket, status, n_tiles);
+    return after_launch("compact_alive_static");
 }
 
 }  // extern "C"

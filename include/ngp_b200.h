@@ -209,6 +209,32 @@ int ngp_render_poses_host(ngp_ctx *ctx, const float *poses_host, uint32_t F, uin
                           float cx, float cy, float dt_gamma, uint32_t max_steps, float bg_color, float *image_host,
                           float *depth_host, void *stream);
 
+/* ---------------------------------------------------------------- differentiable small-batch path
+ * What Estimator.measurement_fn (nav/estimator_helpers.py:191-225: <= 1024 rays, loss.backward() to the pose, 100 iterations)
+ * needs from the CUDA-ray renderer, which upstream cannot give it: raymarching.py:161-230 (march_rays_train) has no backward, so
+ * validate.py:117 falls back to the sampler `run()` whenever gradients w.r.t. rays are wanted.  Here the CUDA-ray render itself is
+ * differentiable w.r.t. rays_o / rays_d.  One warp per ray, no workspace: the backward pass re-marches and re-evaluates.
+ *
+ * forward: the inference result of ngp_render for the same rays (same march / network / compositor functions; a ray takes at most
+ * max_steps samples) plus `finals` [N,4] fp32 (16-byte aligned) = raw (r, g, b, weights_sum) per ray, which the backward pass reads. */
+int ngp_render_diff_forward(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma,
+                            uint32_t max_steps, float bg_color, float *image, float *depth, float *weights_sum,
+                            float *finals, int32_t *samples_per_ray, void *stream);
+/* backward: grad_image [N,3], grad_weights_sum [N] or NULL -> grad_rays_o, grad_rays_d [N,3] (overwritten).  Chain: compositor
+ * (raymarching.cu:606-699; depth carries no gradient there either) -> sigmoid / exp -> colour and density MLPs, input gradients only
+ * (ffmlp.cu backward with calc_grad_inputs; fp16 operands, fp32 accumulation, per-row power-of-two rescaling before every fp16
+ * conversion) -> SH Jacobian (shencoder.cu:126-355) and trilinear hash-grid input gradient (gridencoder.cu:180-223) -> x = o + t d,
+ * dir = d with the sample parameters t held constant (near/far and the marcher are not differentiated upstream either).  The
+ * network and scene registered with ctx must be the ones the forward call saw. */
+int ngp_render_diff_backward(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma,
+                             uint32_t max_steps, float bg_color, const float *finals, const float *grad_image,
+                             const float *grad_weights_sum, float *grad_rays_o, float *grad_rays_d, void *stream);
+/* Backward of ngp_density_forward w.r.t. the points (network_ff.py:76-89 under autograd: gridencoder/grid.py:62-90 with
+ * calc_grad_inputs + ffmlp.py:51-96; the planner's density_fn queries, nav/quad_plot.py:223-300): grad_sigmas [M] -> grad_xyzs [M,3].
+ * geo_feat carries no gradient. */
+int ngp_density_backward(ngp_ctx *ctx, const float *xyzs, const float *grad_sigmas, uint32_t M, int apply_density_scale,
+                         float *grad_xyzs, void *stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -43,6 +43,9 @@ _SIGNATURES = {
     "ngp_network_forward": [_p, _p, _p, _u32, _i32, _p, _p, _p],
     "ngp_network_forward_tc": [_p, _p, _p, _u32, _i32, _p, _p, _p],
     "ngp_density_forward": [_p, _p, _u32, _i32, _p, _p, _p],
+    "ngp_density_backward": [_p, _p, _p, _u32, _i32, _p, _p],
+    "ngp_render_diff_forward": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
+    "ngp_render_diff_backward": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p],
     "ngp_render_uq": [_p, _p, _p, _u32, _f32, _u32, _f32, _p, _p, _p, _p, _p, _p, _p, _u64, _p, _p, _p],
     "ngp_render_sample_rows": [_p, _u32, C.POINTER(_u64)],

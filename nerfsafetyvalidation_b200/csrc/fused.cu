@@ -255,6 +255,8 @@ __device__ __forceinline__ void mlp_rows32(const NetConst &nc, const uint2 *__re
     }
 }
 
+#include "diff_render.cuh"   // differentiable small-batch render + density backward (same building blocks)
+
 // ---------------------------------------------------------------------------------------------- coarse occupancy
 // bit j of the result <- any of the 64 cells with Morton index 64 j .. 64 j + 63 (an aligned 4x4x4 block) is occupied.
 __global__ void k_coarse_occupancy(const unsigned long long *__restrict__ bitfield64, uint32_t n_blocks, uint32_t *__restrict__ coarse) {
@@ -1315,7 +1317,9 @@ struct ngp_ctx {
     bool fast_levels = false;   // every level is a plain dense grid or a power-of-two hash table (what the persistent renderer is built for)
     NetConst nc{};
     uint2 *wpack = nullptr;
+    uint2 *wpack_t = nullptr;     // transposed pack for the input-gradient kernels (diff_render.cuh)
     uint4 *wtc = nullptr;
+    size_t diff_smem[2] = {0, 0}; // dynamic shared memory of k_diff_render<false / true> (== k_density_backward for [1])
     // scene
     const uint8_t *bitfield = nullptr;
     uint32_t cascade = 1, grid_size = 128;
@@ -1377,7 +1381,7 @@ int ngp_ctx_create(ngp_ctx **out) {
 
 int ngp_ctx_destroy(ngp_ctx *c) {
     if (!c) return 0;
-    cudaFree(c->wpack); cudaFree(c->wtc); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
+    cudaFree(c->wpack); cudaFree(c->wpack_t); cudaFree(c->wtc); cudaFree(c->nears); cudaFree(c->fars); cudaFree(c->state[0]); cudaFree(c->state[1]); cudaFree(c->n_emit);
     cudaFree(c->alive[0]); cudaFree(c->alive[1]); cudaFree(c->smp); cudaFree(c->agg[0]); cudaFree(c->agg[1]);
     if (c->h_error) cudaFreeHost(c->h_error);
     cudaFree(c->ctr); cudaFree(c->prof); cudaFree(c->coarse); cudaFree(c->d_o); cudaFree(c->d_d); cudaFree(c->d_img); cudaFree(c->d_depth); cudaFree(c->d_ws); cudaFree(c->d_poses);
@@ -1431,6 +1435,18 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
     if (int rc = after_launch("pack_network")) return rc;
     nc.wpack = c->wpack;
     nc.wpack_count = count;
+    {
+        if (c->wpack_t) { cudaFree(c->wpack_t); c->wpack_t = nullptr; }
+        NGP_CUDA(cudaMalloc(&c->wpack_t, sizeof(uint2) * count));
+        k_pack_network_transposed<<<1, 256, 0, st>>>(reinterpret_cast<const __half *>(w_sigma_f16), nc.nh_sigma,
+                                                     reinterpret_cast<const __half *>(w_color_f16), nc.nh_color, c->wpack_t);
+        if (int rc = after_launch("pack_network_transposed")) return rc;
+        for (int b = 0; b < 2; b++) c->diff_smem[b] = (size_t)count * 8 * (b + 1) + diff::kWarps * diff::warp_smem_bytes(b != 0);
+        NGP_REQUIRE(c->diff_smem[1] <= c->max_smem_optin, "differentiable render: %zu B of shared memory do not fit an SM", c->diff_smem[1]);
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[0]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_density_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
+    }
     {
         const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
         if (c->wtc) { cudaFree(c->wtc); c->wtc = nullptr; }
@@ -1546,6 +1562,67 @@ int ngp_density_forward(ngp_ctx *c, const float *xyzs, uint32_t M, int apply_den
     if (!apply_density_scale) nc.density_scale = 1.0f;
     k_network_forward_tc<true><<<grid, tc::kRows, c->fwd_tc_smem, as_stream(stream)>>>(nc, xyzs, nullptr, M, sigmas, geo_feat_f16, n_tiles);
     return after_launch("density_forward");
+}
+
+// ---- differentiable small-batch render (diff_render.cuh)
+static int diff_args(ngp_ctx *c, const char *what, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps,
+                     float bg_color, diff::DiffArgs &da) {
+    NGP_REQUIRE(c != nullptr && c->has_net && c->has_scene, "%s: ngp_ctx_set_network / ngp_ctx_set_scene have not been called", what);
+    NGP_REQUIRE(max_steps >= 1, "%s: max_steps must be >= 1", what);
+    NGP_DEVPTR(rays_o); NGP_DEVPTR(rays_d);
+    da = diff::DiffArgs{};
+    da.rays_o = rays_o; da.rays_d = rays_d; da.N = N; da.max_steps = max_steps;
+    da.mc = make_march_const(c->nc.bound, dt_gamma, max_steps, c->cascade, c->grid_size, c->bitfield);
+    for (int i = 0; i < 6; i++) da.aabb[i] = c->aabb[i];
+    da.min_near = c->min_near; da.bg = bg_color;
+    da.wpack_t = c->wpack_t;
+    return 0;
+}
+static uint32_t diff_grid(const ngp_ctx *c, uint32_t units) {   // units = rays or 32-point tiles, one per warp
+    const uint32_t want = div_up(units, (uint32_t)diff::kWarps), cap = (uint32_t)c->sm_count * 4u;
+    return want < cap ? want : cap;
+}
+
+int ngp_render_diff_forward(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps,
+                            float bg_color, float *image, float *depth, float *weights_sum, float *finals, int32_t *samples_per_ray,
+                            void *stream) {
+    if (N == 0) return 0;
+    diff::DiffArgs da;
+    if (int rc = diff_args(c, "render_diff_forward", rays_o, rays_d, N, dt_gamma, max_steps, bg_color, da)) return rc;
+    NGP_DEVPTR(image); NGP_DEVPTR(depth); NGP_DEVPTR(weights_sum); NGP_DEVPTR(finals);
+    NGP_REQUIRE((reinterpret_cast<uintptr_t>(finals) & 15) == 0, "render_diff_forward: finals must be 16-byte aligned");
+    if (samples_per_ray) NGP_DEVPTR(samples_per_ray);
+    da.image = image; da.depth = depth; da.weights_sum = weights_sum; da.finals = reinterpret_cast<float4 *>(finals);
+    da.samples_per_ray = samples_per_ray;
+    diff::k_diff_render<false><<<diff_grid(c, N), diff::kThreads, c->diff_smem[0], as_stream(stream)>>>(c->nc, da);
+    return after_launch("render_diff_forward");
+}
+
+int ngp_render_diff_backward(ngp_ctx *c, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma, uint32_t max_steps,
+                             float bg_color, const float *finals, const float *grad_image, const float *grad_weights_sum,
+                             float *grad_rays_o, float *grad_rays_d, void *stream) {
+    if (N == 0) return 0;
+    diff::DiffArgs da;
+    if (int rc = diff_args(c, "render_diff_backward", rays_o, rays_d, N, dt_gamma, max_steps, bg_color, da)) return rc;
+    NGP_DEVPTR(finals); NGP_DEVPTR(grad_image); NGP_DEVPTR(grad_rays_o); NGP_DEVPTR(grad_rays_d);
+    NGP_REQUIRE((reinterpret_cast<uintptr_t>(finals) & 15) == 0, "render_diff_backward: finals must be 16-byte aligned");
+    if (grad_weights_sum) NGP_DEVPTR(grad_weights_sum);
+    da.finals = const_cast<float4 *>(reinterpret_cast<const float4 *>(finals));
+    da.g_image = grad_image; da.g_ws = grad_weights_sum; da.g_o = grad_rays_o; da.g_d = grad_rays_d;
+    diff::k_diff_render<true><<<diff_grid(c, N), diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(c->nc, da);
+    return after_launch("render_diff_backward");
+}
+
+int ngp_density_backward(ngp_ctx *c, const float *xyzs, const float *grad_sigmas, uint32_t M, int apply_density_scale, float *grad_xyzs,
+                         void *stream) {
+    NGP_REQUIRE(c != nullptr && c->has_net, "density_backward: ngp_ctx_set_network has not been called");
+    if (M == 0) return 0;
+    NGP_DEVPTR(xyzs); NGP_DEVPTR(grad_sigmas); NGP_DEVPTR(grad_xyzs);
+    NetConst nc = c->nc;
+    if (!apply_density_scale) nc.density_scale = 1.0f;
+    diff::k_density_backward<<<diff_grid(c, div_up(M, 32u)), diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(nc, c->wpack_t, xyzs, grad_sigmas,
+                                                                                                                   M, grad_xyzs);
+    return after_launch("density_backward");
 }
 
 static int ensure_workspace(ngp_ctx *c, uint32_t N) {

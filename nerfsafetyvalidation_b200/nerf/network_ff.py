@@ -137,6 +137,11 @@ class NeRFNetwork(NeRFRenderer):
         if getattr(self, "fused_density", True) and self._configure_native(self._native):
             _cabi.require_cuda(x)
             prefix = x.shape[:-1]
+            if torch.is_grad_enabled() and x.requires_grad:
+                # the planner's density_fn under autograd (nav/quad_plot.py:223-300): d sigma / d x from ngp_density_backward
+                from .autograd import DensityPoints
+                sigma, geo = DensityPoints.apply(x.float().contiguous().view(-1, 3), self)
+                return {"sigma": sigma.view(*prefix), "geo_feat": geo.view(*prefix, self.geo_feat_dim)}
             x = x.float().contiguous().view(-1, 3)
             M = x.shape[0]
             sigma = torch.empty(M, dtype=torch.float32, device=x.device)

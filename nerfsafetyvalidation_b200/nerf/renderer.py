@@ -243,6 +243,14 @@ class NeRFRenderer(nn.Module):
             bg_color = 1
         fused = self.fused if fused is None else fused
         scalar_bg = not torch.is_tensor(bg_color)
+        if torch.is_grad_enabled() and (rays_o.requires_grad or rays_d.requires_grad):
+            # gradients w.r.t. the rays (Estimator.measurement_fn, nav/estimator_helpers.py:191-225): upstream only the sampler
+            # path run() provides them (raymarching.py:161-230 has no backward); here the CUDA-ray render itself does
+            if perturb or not scalar_bg or not self._configure_native(self._native):
+                raise NotImplementedError("run_cuda: gradients w.r.t. rays need perturb=False, a scalar bg_color and the fusable NGP network")
+            from .autograd import RenderRays
+            image, depth, weights_sum = RenderRays.apply(rays_o, rays_d, self, float(dt_gamma), int(max_steps), float(bg_color))
+            return {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum, "sigmas": None, "rgbs": None}
         if fused and not perturb and scalar_bg and self._configure_native(self._native):
             return self._run_fused(rays_o, rays_d, prefix, N, device, float(dt_gamma), int(max_steps), float(bg_color), return_stats,
                                    return_uq)

@@ -70,7 +70,12 @@ def build(name: str) -> str:
 # The reference's own Python on the path, unmodified, so that the GPU box (which has no /root/reference) can run its methods on the
 # rebuilt extensions: tests/refext.reference_renderer_class() imports nerf/renderer.py from here behind three stub modules.  Like the
 # .so files these are build OUTPUTS: oracle/_ref/ is git-ignored, nothing of it enters the repository's history.
-PYREF = ["nerf/renderer.py", "nerf/network_ff.py", "validate.py"]
+PYREF = ["nerf/renderer.py", "nerf/network_ff.py", "validate.py",
+         # the reference's autograd Functions and module glue (tests/refext.reference_training_stack(): the gradient oracle of
+         # the differentiable path runs the reference's OWN backward kernels through its OWN Python)
+         "encoding.py", "activation.py", "gridencoder/__init__.py", "gridencoder/grid.py", "shencoder/__init__.py",
+         "shencoder/sphere_harmonics.py", "ffmlp/__init__.py", "ffmlp/ffmlp.py", "raymarching/__init__.py",
+         "raymarching/raymarching.py"]
 
 
 def copy_python():

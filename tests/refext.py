@@ -163,6 +163,70 @@ def reference_renderer_class():
     return mod.NeRFRenderer
 
 
+def reference_training_stack():
+    """The reference's OWN Python for the differentiable pieces, imported unmodified from oracle/_ref/pyref on top of the rebuilt
+    extensions: returns (a constructor of nerf/network_ff.py's NeRFNetwork on the reference's gridencoder / shencoder / ffmlp packages and its
+    own nerf/renderer.py, the reference's `raymarching` module with march_rays_train / composite_rays_train).  The packages'
+    `try: import _<ext> as _backend` (e.g. gridencoder/grid.py:9-12) finds the rebuilt .so files through sys.modules.  Everything is
+    imported under private module names and the process-wide names are restored, so the product's packages are not shadowed.
+    None when the copies or an extension are missing."""
+    import sys
+    import types
+    root = os.path.join(REF_DIR, "pyref")
+    if "ngp_ref_train" in _mods:
+        return _mods["ngp_ref_train"]
+    if not all(available(n) for n in ("_raymarching", "_gridencoder", "_shencoder", "_ffmlp")) or \
+            not os.path.exists(os.path.join(root, "gridencoder", "grid.py")):
+        return None
+    names = ["_raymarching", "_gridencoder", "_shencoder", "_ffmlp", "raymarching", "gridencoder", "shencoder", "ffmlp", "encoding",
+             "activation", "nerf", "nerf.renderer", "nerf.network_ff", "nerf.utils", "trimesh", "turtle"]
+    subs = ["raymarching.raymarching", "gridencoder.grid", "shencoder.sphere_harmonics", "ffmlp.ffmlp"]
+    saved = {k: sys.modules.get(k) for k in names + subs}
+    for k in names + subs:
+        sys.modules.pop(k, None)
+    for n in ("_raymarching", "_gridencoder", "_shencoder", "_ffmlp"):
+        sys.modules[n] = ext(n)
+    sys.modules["trimesh"] = saved["trimesh"] or types.ModuleType("trimesh")
+    if "turtle" not in sys.modules:   # ffmlp/ffmlp.py:2 carries a stray `from turtle import backward, forward` (needs tkinter); unused
+        turtle = types.ModuleType("turtle")
+        turtle.backward = turtle.forward = None
+        sys.modules["turtle"] = turtle
+    utils = types.ModuleType("nerf.utils")
+    utils.custom_meshgrid = lambda *a: torch.meshgrid(*a, indexing="ij")       # nerf/utils.py:28-33
+    pkg = types.ModuleType("nerf")
+    pkg.__path__ = [os.path.join(root, "nerf")]
+    sys.modules["nerf"], sys.modules["nerf.utils"] = pkg, utils
+    sys.path.insert(0, root)
+    try:
+        import importlib
+        rm = importlib.import_module("raymarching")
+        net = importlib.import_module("nerf.network_ff")
+        lazy = {k: importlib.import_module(k) for k in ("gridencoder", "shencoder", "ffmlp")}   # encoding.py:60-70 imports them per call
+
+        def make(**kwargs):
+            """NeRFNetwork(**kwargs) with the reference's encoder packages visible to encoding.get_encoder's call-time imports."""
+            held = {k: sys.modules.get(k) for k in lazy}
+            sys.modules.update(lazy)
+            try:
+                return net.NeRFNetwork(**kwargs)
+            finally:
+                for k, v in held.items():
+                    if v is None:
+                        sys.modules.pop(k, None)
+                    else:
+                        sys.modules[k] = v
+        out = (make, rm)
+    finally:
+        sys.path.remove(root)
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    _mods["ngp_ref_train"] = out
+    return out
+
+
 class RefModel:
     """Holds what network_ff.NeRFNetwork holds, as device tensors (half copies = what autocast would produce)."""
 

@@ -1,0 +1,278 @@
+"""GPU tests of the differentiable small-batch path (include/ngp_b200.h: ngp_render_diff_forward /
+ngp_render_diff_backward / ngp_density_backward), through the reference-facing surface: `model.render(rays_o, rays_d, ...)` with
+rays that require grad, and `model.density(x)` with points that require grad.
+
+Oracles:
+  * forward: the inference renderer (already held to the reference's extensions by test_gpu_parity.py / test_gpu_configs.py);
+  * derivative: tests/diff_oracle.py, the fp64 autograd definition (pinned on the CPU by tests/test_diff_oracle.py);
+  * the reference's OWN backward kernels (grid_encode_backward + dy_dx, sh_encode_backward, ffmlp_backward, composite_rays_train_backward)
+    driven by its OWN Python (tests/refext.reference_training_stack()), with the one line the reference lacks, x = o + t d, in torch.
+Tolerances are relative L2 errors of the gradient over the batch; they are written next to each assert with what was measured.
+"""
+import numpy as np
+import pytest
+import torch
+
+from nerfsafetyvalidation_b200 import raymarching as our_rm
+from nerfsafetyvalidation_b200 import synthetic as syn
+from tests import diff_oracle as dorc
+from tests import refext
+
+pytestmark = pytest.mark.gpu
+
+N_RAYS, MAX_STEPS = 384, 1024
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-300))
+
+
+def all_active_weights():
+    """Variant "C": a network with NO ReLU kinks on the data -- non-negative table and weights, so every hidden unit is active at
+    every sample.  The derivative of a ReLU network is piecewise constant: wherever the kernels' fp16-rounded forward and the unrounded
+    fp64 definition disagree on the sign of one pre-activation (about 1 unit in 1000 with variants A / B), that sample's gradient
+    differs by ~1/sqrt(active units).  Variant C removes that effect and leaves the arithmetic of the backward chain itself
+    (compositor, sigmoid / exp, both MLPs, SH Jacobian, trilinear input gradient, x = o + t d) to be compared tightly."""
+    w = dict(syn.ngp_weights(0, variant="B"))
+    w["density_scale"] = 1.0
+    table = np.abs(w["table_f32"]).astype(np.float16)
+    ws = np.abs(w["w_sigma_f32"]).astype(np.float32)
+    ws[2048:-1024] *= 0.1                               # hidden activations stay O(1) ...
+    ws[-1024:] *= 0.2                                   # ... and h0 ~ 1.7: sigma ~ 5, weights_sum ~ 0.75 after ~80 samples
+    wc = np.abs(w["w_color_f32"]).astype(np.float32)
+    wc[2048:] *= 0.1                                    # keeps the pre-sigmoid output O(1)
+    ws, wc = ws.astype(np.float16), wc.astype(np.float16)
+    w.update(table=table, table_f32=table.astype(np.float32), w_sigma=ws, w_sigma_f32=ws.astype(np.float32), w_color=wc,
+             w_color_f32=wc.astype(np.float32))
+    return w
+
+
+@pytest.fixture(scope="module")
+def world(cuda, scene):
+    bitfield, grid = scene
+    o, d = syn.pinhole_rays(syn.orbit_pose(), 96, 96)
+    pick = np.random.default_rng(11).permutation(o.shape[0])[:N_RAYS]
+    o, d = np.ascontiguousarray(o[pick], np.float32), np.ascontiguousarray(d[pick], np.float32)
+    o[-16:], d[-16:] = 3.0, np.float32(1 / np.sqrt(3))          # rays that miss the box: background pixels, NaN depth, zero gradient
+    o[-32:-16] = np.float32([0.0, 0.9, 0.0])                    # rays from inside the box through empty space only
+    d[-32:-16] = np.float32([0.0, 1.0, 0.0])
+    out = dict(o=torch.from_numpy(o).to(cuda), d=torch.from_numpy(d).to(cuda), bitfield=bitfield)
+    for var in "ABC":
+        w = all_active_weights() if var == "C" else syn.ngp_weights(0, variant=var)
+        out["w" + var] = w
+        out["m" + var] = syn.build_model(w, bitfield, grid, device=cuda)
+    out["G"] = torch.randn(N_RAYS, 3, generator=torch.Generator().manual_seed(3)).to(cuda)
+    return out
+
+
+def our_grads(model, o, d, G, g_ws=None, **kw):
+    o = o.clone().requires_grad_(True)
+    d = d.clone().requires_grad_(True)
+    res = model.render(o[None], d[None], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS, **kw)
+    loss = (res["image"][0] * G).sum()
+    if g_ws is not None:
+        loss = loss + (res["weights_sum"] * g_ws).sum()
+    loss.backward()
+    return res, o.grad, d.grad
+
+
+def marched_samples(model, o, d):
+    """(t, dt, count) float64 [N,S] of every ray's samples, from the stand-alone marcher (bit-exact with the reference's)."""
+    N = o.shape[0]
+    nears, fars = our_rm.near_far_from_aabb(o, d, model.aabb_infer, model.min_near)
+    alive = torch.arange(N, dtype=torch.int32, device=o.device)
+    _, _, deltas = our_rm.march_rays(N, MAX_STEPS, alive, nears.clone(), o, d, model.bound, model.density_bitfield, model.cascade,
+                                     model.grid_size, nears, fars, -1, False, 0, MAX_STEPS)
+    t, dt, count = dorc.samples_from_deltas(deltas, nears, N, MAX_STEPS)
+    S = max(int(count.max()), 1)
+    return t[:, :S].contiguous(), dt[:, :S].contiguous(), count
+
+
+@pytest.mark.parametrize("var", ["A", "B", "C"])
+def test_forward_equals_inference_render(world, var):
+    model, o, d = world["m" + var], world["o"], world["d"]
+    with torch.no_grad():
+        ref = model.render(o[None], d[None], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
+    res, _, _ = our_grads(model, o, d, world["G"])
+    assert res["image"].requires_grad and not res["depth"].requires_grad
+    # same march / network / compositor functions, mma.sync instead of tcgen05 accumulation order: measured <= 3e-6
+    assert float((res["image"] - ref["image"]).abs().max()) < 1e-4
+    assert float((res["weights_sum"] - ref["weights_sum"]).abs().max()) < 1e-4
+    dm = (res["depth"] - ref["depth"]).abs()
+    assert float(dm[~torch.isnan(dm)].max()) < 1e-4 and torch.equal(torch.isnan(res["depth"]), torch.isnan(ref["depth"]))
+
+
+# aggregate relative L2 error of the batch's gradient / median over rays of the per-ray relative error
+# / |median over rays of (g . g_def) / (g_def . g_def) - 1| (a systematic scale error would show here)
+RAY_TOL = {"A": (1e-1, 5e-2, 2e-2), "B": (1e-1, 3e-2, 5e-3), "C": (5e-2, 5e-3, 5e-3)}
+
+
+def per_row_rel(a, b):
+    return (a.double() - b.double()).norm(dim=-1) / b.double().norm(dim=-1).clamp_min(1e-300)
+
+
+@pytest.mark.parametrize("var", ["A", "B", "C"])
+def test_ray_gradients_match_fp64_definition(world, var, cuda):
+    model, w, o, d, G = world["m" + var], world["w" + var], world["o"], world["d"], world["G"]
+    g_ws = torch.linspace(-1, 1, N_RAYS, device=cuda)
+    _, go, gd = our_grads(model, o, d, G, g_ws)
+    t, dt, count = marched_samples(model, o, d)
+    assert int((count > 0).sum()) > N_RAYS // 4
+    net = dorc.Net(w, device=cuda)
+    od, dd = o.double().requires_grad_(True), d.double().requires_grad_(True)
+    image, ws = dorc.render(net, od, dd, t, dt, count, bg=1.0)
+    ((image * G.double()).sum() + (ws * g_ws.double()).sum()).backward()
+    missed = count == 0
+    assert int(missed.sum()) >= 16
+    assert float(go[missed].abs().max()) == 0.0 and float(gd[missed].abs().max()) == 0.0
+    eo, ed = rel_l2(go, od.grad), rel_l2(gd, dd.grad)
+    hit = ~missed
+    mo, md = float(per_row_rel(go, od.grad)[hit].median()), float(per_row_rel(gd, dd.grad)[hit].median())
+    print(f"variant {var}: rel L2 error d/d rays_o {eo:.3e}, d/d rays_d {ed:.3e}; per-ray median {mo:.3e} / {md:.3e}; |g_o| {float(od.grad.norm()):.3e}")
+    ratio = float(((go.double() * od.grad).sum(-1) / (od.grad * od.grad).sum(-1).clamp_min(1e-300))[hit].median())
+    print(f"variant {var}: median projection ratio {ratio:.6f}")
+    # measured (B200), aggregate / per-ray median: A 4.0e-2 / 3.2e-2, B 4.0e-2 / 6e-3 (ReLU sign disagreements between the fp16-rounded
+    # forward and the fp64 definition, see all_active_weights; the reference's own backward kernels sit at 6e-2 from the same
+    # definition), C 3.0e-2 / 1e-3 (what is left in C's aggregate: samples that the fp32 march puts on the other side of a grid-cell
+    # face than the fp64 restatement of t -- the trilinear derivative jumps there); projection ratio 1.00005 (B), 0.99998 (C)
+    tol, tol_med, tol_ratio = RAY_TOL[var]
+    assert eo < tol and ed < tol
+    assert mo < tol_med and md < tol_med
+    assert abs(ratio - 1) < tol_ratio
+
+
+def test_gradient_is_independent_of_the_loss_scale(world):
+    """Every fp32 -> fp16 conversion of the backward is preceded by a per-row power-of-two renormalisation: scaling the upstream
+    gradient by 2^-24 (a pixel loss's magnitude, where a plain half backward underflows) scales the result by exactly 2^-24."""
+    model, o, d, G = world["mB"], world["o"], world["d"], world["G"]
+    _, go, gd = our_grads(model, o, d, G)
+    _, go_s, gd_s = our_grads(model, o, d, G * 2.0 ** -24)
+    assert float(go.abs().max()) > 0
+    assert torch.equal(go_s * 2.0 ** 24, go) and torch.equal(gd_s * 2.0 ** 24, gd)
+
+
+@pytest.mark.parametrize("var", ["A", "B", "C"])
+def test_density_gradient(world, var, cuda):
+    model, w = world["m" + var], world["w" + var]
+    g = torch.Generator().manual_seed(8)
+    x = (torch.rand(5000, 3, generator=g) * 2 - 1)
+    x[:8] = 1.0
+    x[8:16, 1] = 1.5                                          # outside: sigma = exp(h(0)), gradient 0
+    x = x.to(cuda)
+    gs = torch.randn(5000, generator=g).to(cuda)
+    xr = x.clone().requires_grad_(True)
+    out = model.density(xr)
+    assert out["sigma"].requires_grad and not out["geo_feat"].requires_grad
+    with torch.no_grad():
+        plain = model.density(x)
+    assert torch.equal(out["sigma"].detach(), plain["sigma"]) and torch.equal(out["geo_feat"], plain["geo_feat"])
+    (out["sigma"] * gs).sum().backward()
+    net = dorc.Net(w, device=cuda)
+    xd = x.double().requires_grad_(True)
+    sig, _ = net.density(xd)
+    (sig * gs.double()).sum().backward()
+    assert float(xr.grad[8:16].abs().max()) == 0.0
+    e = rel_l2(xr.grad, xd.grad)
+    med = float(per_row_rel(xr.grad[16:], xd.grad[16:]).median())
+    print(f"variant {var}: density gradient rel L2 error {e:.3e}, per-point median {med:.3e}")
+    # measured (B200): A 4.1e-2, B 1.6e-2 (ReLU sign disagreements on a few points, see all_active_weights), C 4.1e-3; medians 3e-4 .. 4e-4
+    assert e < (2e-2 if var == "C" else 1e-1)
+    assert med < 5e-3
+
+
+needs_train_stack = pytest.mark.skipif(
+    not all(refext.available(n) for n in ("_raymarching", "_gridencoder", "_shencoder", "_ffmlp")),
+    reason="oracle/_ref extensions not built (python oracle/build_ref.py)")
+
+
+def build_reference_model(w, ours, device):
+    """The reference's NeRFNetwork (its own network_ff.py / renderer.py / gridencoder / shencoder / ffmlp Python on the rebuilt extensions)
+    carrying our model's state dict, in train mode (ffmlp.py:162: only the training kernels keep what the backward needs)."""
+    stack = refext.reference_training_stack()
+    assert stack is not None, "oracle/_ref/pyref is incomplete (python oracle/build_ref.py)"
+    Net, rm = stack
+    ref = Net(encoding="hashgrid", bound=w["bound"], cuda_ray=True, density_scale=w["density_scale"], min_near=0.2, density_thresh=10.0,
+              bg_radius=-1, num_layers=w["num_layers"], num_layers_color=w["num_layers_color"])
+    missing = ref.load_state_dict(ours.state_dict(), strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    return ref.to(device).train(), rm
+
+
+def reference_parts_grads(ref, rm, o, d, G, g_ws):
+    """The reference's training-mode CUDA-ray render (nerf/renderer.py:285-327: march_rays_train -> NeRFNetwork.forward under autocast
+    -> composite_rays_train) through its OWN Python and backward kernels, with the sample positions rebuilt as x = o + t d in torch so
+    that autograd reaches the rays (march_rays_train returns xyzs without a backward, raymarching.py:161-230)."""
+    device = o.device
+    nears, fars = rm.near_far_from_aabb(o, d, ref.aabb_infer, ref.min_near)
+    xyzs, dirs, deltas, rays = rm.march_rays_train(o, d, ref.bound, ref.density_bitfield, ref.cascade, ref.grid_size, nears, fars, None, -1,
+                                                   False, 128, True, 0, MAX_STEPS)
+    M = xyzs.shape[0]
+    order = torch.argsort(rays[:, 1])
+    idx, cnt = rays[order, 0].long(), rays[order, 2].long()
+    total = int(cnt.sum())
+    rid = torch.zeros(M, dtype=torch.long, device=device)
+    rid[:total] = torch.repeat_interleave(idx, cnt)
+    live = torch.arange(M, device=device) < total
+    t = (((xyzs - o[rid]) * d[rid]).sum(-1) / (d[rid] * d[rid]).sum(-1)) * live         # the parameter each sample was taken at
+    orq, drq = o.clone().requires_grad_(True), d.clone().requires_grad_(True)
+    x = orq[rid] + t[:, None] * drq[rid]
+    assert float((x.detach() - xyzs)[live].abs().max()) < 1e-5
+    with torch.autocast("cuda", dtype=torch.float16):
+        sigmas, rgbs = ref(x, drq[rid])
+        sigmas = ref.density_scale * sigmas
+        ws, depth, image = rm.composite_rays_train(sigmas, rgbs, deltas, rays)
+        image = image + (1 - ws).unsqueeze(-1) * 1.0
+    ((image * G).sum() + (ws * g_ws).sum()).backward()
+    return image.detach(), orq.grad, drq.grad
+
+
+@needs_train_stack
+@pytest.mark.parametrize("var", ["A", "B", "C"])
+def test_ray_gradients_against_the_reference_backward_kernels(world, var, cuda):
+    model, w, o, d, G = world["m" + var], world["w" + var], world["o"], world["d"], world["G"]
+    g_ws = torch.linspace(-1, 1, N_RAYS, device=cuda)
+    res, go, gd = our_grads(model, o, d, G, g_ws)
+    ref, rm = build_reference_model(w, model, cuda)
+    img_ref, go_ref, gd_ref = reference_parts_grads(ref, rm, o, d, G, g_ws)
+    assert float((res["image"][0] - img_ref).abs().max()) < 1e-3          # north_star's image tolerance
+    # the fp64 definition, to say which side the difference comes from
+    t, dt, count = marched_samples(model, o, d)
+    net = dorc.Net(w, device=cuda)
+    od, dd = o.double().requires_grad_(True), d.double().requires_grad_(True)
+    image, ws = dorc.render(net, od, dd, t, dt, count, bg=1.0)
+    ((image * G.double()).sum() + (ws * g_ws.double()).sum()).backward()
+    ours_ref = (rel_l2(go, go_ref), rel_l2(gd, gd_ref))
+    ours_def = (rel_l2(go, od.grad), rel_l2(gd, dd.grad))
+    ref_def = (rel_l2(go_ref, od.grad), rel_l2(gd_ref, dd.grad))
+    print(f"variant {var}: ours vs reference kernels {ours_ref[0]:.3e} / {ours_ref[1]:.3e}; ours vs fp64 {ours_def[0]:.3e} / {ours_def[1]:.3e}; "
+          f"reference kernels vs fp64 {ref_def[0]:.3e} / {ref_def[1]:.3e}")
+    # the reference's backward is fp16 throughout (half dy_dx, half backward buffers) and its forward rounds differently from ours, so
+    # with A / B both sides disagree with the fp64 definition -- and with each other -- on a few ReLU signs: measured (B200) ours vs
+    # reference 6.6e-2, reference vs fp64 6.2e-2, ours vs fp64 4.0e-2.  Variant C (no kinks) compares the arithmetic alone: ours vs
+    # the reference's kernels 5.5e-3 / 4.9e-3, while BOTH sit at 3.0e-2 from the fp64 definition (its fp64 restatement of t puts a few
+    # samples on the other side of a grid-cell face than the fp32 x both kernel sets use).
+    assert max(ours_ref) < (2e-2 if var == "C" else 1.5e-1)
+    assert max(ours_def) <= max(ref_def) * 1.5 + 1e-3
+
+
+@needs_train_stack
+@pytest.mark.parametrize("var", ["A", "B", "C"])
+def test_density_gradient_against_the_reference_backward_kernels(world, var, cuda):
+    """NeRFNetwork.density under autograd, reference side: gridencoder/grid.py:62-90 (dy_dx) + ffmlp.py:51-96 on the rebuilt kernels."""
+    model, w = world["m" + var], world["w" + var]
+    ref, _ = build_reference_model(w, model, cuda)
+    g = torch.Generator().manual_seed(9)
+    x = (torch.rand(4096, 3, generator=g) * 2 - 1).to(cuda)
+    gs = torch.randn(4096, generator=g).to(cuda)
+    xr = x.clone().requires_grad_(True)
+    (model.density(xr)["sigma"] * gs).sum().backward()
+    xq = x.clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.float16):
+        sig = ref.density(xq)["sigma"]
+    (sig.float() * gs).sum().backward()
+    e = rel_l2(xr.grad, xq.grad)
+    med = float(per_row_rel(xr.grad, xq.grad).median())
+    print(f"variant {var}: density gradient, ours vs reference kernels {e:.3e}, per-point median {med:.3e}")
+    # measured (B200): A 7.9e-2, B 5.2e-2 (ReLU sign disagreements on a few points + the reference's half dy_dx), C 9.8e-4
+    assert e < (5e-3 if var == "C" else 1.5e-1)
+    assert med < 2e-2

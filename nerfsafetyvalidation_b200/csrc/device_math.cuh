@@ -209,6 +209,36 @@ __device__ __forceinline__ bool march_probe(const MarchConst &m, float ox, float
     return false;
 }
 
+// The cell test of march_probe WITHOUT advancing the ray (same expressions, operation for operation): is the cell under the ray at t
+// occupied?  If not, tt <- the parameter at which the marcher's skip loop stops stepping (t + max(0, distance to the cell's exit),
+// raymarching.cu:795-806).  For callers that test many candidate parameters of ONE ray in parallel (diff_render.cuh).
+__device__ __forceinline__ bool march_peek(const MarchConst &m, float ox, float oy, float oz, const RayDir &rd, float t, float &tt) {
+    const bool one_level = m.cm1f == 0.0f;
+    const float x = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(rd.dx, t, ox)));
+    const float y = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(rd.dy, t, oy)));
+    const float z = fminf(m.bound, fmaxf(-m.bound, __fmaf_rn(rd.dz, t, oz)));
+    int level = 0;
+    if (!one_level) {
+        const float dt = sample_dt(m, t);
+        const int l_pos = mip_level(fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))), m.cm1f);
+        const int l_dt = mip_level(__fmul_rn(__fmul_rn(dt, m.Hf), 0.5f), m.cm1f);
+        level = max(l_pos, l_dt);
+    }
+    const float mip_bound = m.mip_b[level];
+    const float mip_rbound = m.mip_rb[level];
+    const int nx = cell_coord(x, mip_rbound, m);
+    const int ny = cell_coord(y, mip_rbound, m);
+    const int nz = cell_coord(z, mip_rbound, m);
+    const uint32_t idx = (uint32_t)__fmaf_rn(m.H3f, (float)level, (float)morton3d(nx, ny, nz));
+    tt = t;
+    if ((__ldg(m.grid + (idx >> 3)) >> (idx & 7)) & 1) return true;
+    const float tx = cell_exit(nx, rd.sx, mip_bound, x, rd.rdx, m);
+    const float ty = cell_exit(ny, rd.sy, mip_bound, y, rd.rdy, m);
+    const float tz = cell_exit(nz, rd.sz, mip_bound, z, rd.rdz, m);
+    tt = __fadd_rn(t, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+    return false;
+}
+
 // Marches one ray from t for up to n_step occupied samples (one reference chunk).  emit(step, x, y, z, dt, delta_t) is
 // called per sample.  Returns the number of samples emitted.
 template <class Emit>

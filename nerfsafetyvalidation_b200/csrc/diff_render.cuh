@@ -2,7 +2,7 @@
 // mma.sync building blocks): what Estimator.measurement_fn (nav/estimator_helpers.py:191-225, <= 1024 rays, loss.backward() on the
 // pose) and the planner's density queries (nav/quad_plot.py:223-300 through validate.py:288) need from the CUDA-ray path.
 //
-//   k_diff_render<false>   forward: one WARP per ray -- march (lane 0, the reference's loop body) -> 32-sample chunks -> hash grid ->
+//   k_diff_render<false>   forward: one WARP per ray -- march (32 candidate parameters per step, see march_window) -> 32-sample chunks -> hash grid ->
 //                          both MLPs (mma.sync, fp32 accumulate) -> front-to-back compositing with the T < 1e-4 stop.  Same functions
 //                          as the inference renderer, sample for sample.
 //   k_diff_render<true>    backward: re-runs the forward of every chunk (nothing but 16 B per ray is kept between the passes) and
@@ -119,13 +119,15 @@ __device__ __forceinline__ void net_forward(const uint2 *__restrict__ w_first, c
     mlp_layer<2, 2, 8>(A0, w_first, lane, C);
     masks[0] = relu_mask(C);
     relu_to_frag<2, 8>(C, A);
+    // rolled: one copy of the 64-MMA hidden layer in the instruction stream (these kernels run 4 warps per CTA; code size, not
+    // issue rate, is what an unrolled chain of layers would cost them)
+#pragma unroll 1
+    for (uint32_t k = 0; k < nh; k++) {
+        mlp_layer<2, 4, 8>(A, w_hidden + (size_t)k * 1024, lane, C);
+        const uint64_t mk = relu_mask(C);
 #pragma unroll
-    for (int k = 0; k < kMaxHidden - 1; k++) {
-        if ((uint32_t)k < nh) {
-            mlp_layer<2, 4, 8>(A, w_hidden + (size_t)k * 1024, lane, C);
-            masks[k + 1] = relu_mask(C);
-            relu_to_frag<2, 8>(C, A);
-        }
+        for (int i = 1; i < kMaxHidden; i++) masks[i] = (uint32_t)i == k + 1 ? mk : masks[i];
+        relu_to_frag<2, 8>(C, A);
     }
     mlp_layer<2, 4, 2>(A, w_last, lane, O);
 }
@@ -180,12 +182,13 @@ __device__ __forceinline__ void net_backward(const uint2 *__restrict__ wt_first,
     float C[2][8][4];
     uint32_t A[2][4][4];
     mlp_layer<2, 1, 8>(Aout, wt_last, lane, C);       // d(last hidden activation)
+#pragma unroll 1
+    for (int k = (int)nh - 1; k >= 0; k--) {
+        uint64_t mk = masks[1];
 #pragma unroll
-    for (int k = kMaxHidden - 2; k >= 0; k--) {
-        if ((uint32_t)k < nh) {
-            grad_to_frag<8, true>(C, masks[k + 1], A, rs);
-            mlp_layer<2, 4, 8>(A, wt_hidden + (size_t)k * 1024, lane, C);
-        }
+        for (int i = 2; i < kMaxHidden; i++) mk = i == k + 1 ? masks[i] : mk;
+        grad_to_frag<8, true>(C, mk, A, rs);
+        mlp_layer<2, 4, 8>(A, wt_hidden + (size_t)k * 1024, lane, C);
     }
     grad_to_frag<8, true>(C, masks[0], A, rs);
     mlp_layer<2, 4, 4>(A, wt_first, lane, Cin);
@@ -211,7 +214,7 @@ __device__ __forceinline__ void grid_input_grad(const NetConst &nc, float x, flo
     gx = gy = gz = 0.0f;
     float u0, u1, u2;
     if (!encode_unit(nc, x, y, z, u0, u1, u2)) return;
-#pragma unroll 1
+#pragma unroll 4
     for (int l = 0; l < 16; l++) {
         const LevelConst &lc = nc.lv[l];
         const float scale = lc.scale;
@@ -361,6 +364,82 @@ __device__ __forceinline__ void backward_chunk(const NetConst &nc, const uint2 *
                 ws.denc[(mt * 16 + g + 8 * (e >> 1)) * kDencStride + nt * 8 + 2 * t + (e & 1)] = Cenc[mt][nt][e] / rs[mt][e >> 1];
 }
 
+// ---------------------------------------------------------------------------------------------- march, one warp per ray
+// The reference's marcher (raymarching.cu:754-812) visits a SUBSET of one fixed sequence of parameters per ray, whatever the
+// occupancy: t_0 = near, t_{k+1} = t_k + dt(t_k) -- an occupied cell advances by dt(t), an empty one repeats the same step until the
+// cell's exit is passed.  So a warp tests 32 consecutive candidates of its ray at once (one occupancy load per lane, all in flight)
+// and then replays the marcher's control flow on the 32 answers: an occupied candidate is a sample and hands over to the next
+// candidate; an empty one hands over to the first later candidate at or beyond its cell's exit.  Same samples, same (t, delta_t), as
+// the serial loop -- without 32 dependent loads per chunk.
+struct MarchState {
+    float t_base;    // first candidate of the next window
+    float last_t;    // the marcher's last_t: the parameter after the previous sample
+    float skip_to;   // an empty cell's exit that lies beyond the previous window (-FLT_MAX: none)
+    bool done;       // the ray has left [near, far) or used up its sample budget
+};
+
+// Tests the next 32 candidates and appends the samples found, in order, to ws.smp[have ..); returns the new fill <= 32.  `budget`
+// = samples the ray may still take (max_steps).  When the window holds more samples than the chunk has room for, the march is
+// rewound to the candidate after the last sample taken (the marcher visits it next in any case).
+__device__ __forceinline__ uint32_t march_window(const MarchConst &m, float ox, float oy, float oz, const RayDir &rd, float far,
+                                                 uint32_t budget, uint32_t have, MarchState &st, const WarpSmem &ws, int lane) {
+    constexpr uint32_t kFull = 0xffffffffu;
+    float cur = st.t_base, tk = 0.f, tn = 0.f;
+#pragma unroll 4
+    for (int i = 0; i < 32; i++) {                     // every lane walks the sequence; lane i keeps candidate i and its successor
+        const float nx = __fadd_rn(cur, sample_dt(m, cur));
+        if (lane == i) { tk = cur; tn = nx; }
+        cur = nx;
+    }
+    const bool valid = tk < far;
+    float tt = tk;
+    bool occ = false;
+    if (valid) occ = march_peek(m, ox, oy, oz, rd, tk, tt);
+    const uint32_t occ_mask = __ballot_sync(kFull, occ), valid_mask = __ballot_sync(kFull, valid);
+    const uint32_t reach = __ballot_sync(kFull, tk >= st.skip_to);
+    int j = reach ? __ffs(reach) - 1 : 32;
+    float carry = j < 32 ? -FLT_MAX : st.skip_to;
+    uint32_t visited = 0;
+    bool done = false;
+    while (j < 32) {                                   // warp-uniform replay of the marcher's hand-overs
+        if (!((valid_mask >> j) & 1u)) { done = true; break; }
+        if ((occ_mask >> j) & 1u) {                    // a run of occupied candidates: each is visited and hands over to the next
+            const uint32_t rest = ~occ_mask & (kFull << j);
+            const int e = rest ? __ffs(rest) - 1 : 32;
+            visited |= (e == 32 ? kFull : ((1u << e) - 1u)) & (kFull << j);
+            j = e;
+        } else {                                       // empty cell: first later candidate at or beyond the cell's exit (at least one step)
+            const float t_exit = __shfl_sync(kFull, tt, j);
+            const uint32_t later = __ballot_sync(kFull, tk >= t_exit) & (j == 31 ? 0u : (kFull << (j + 1)));
+            if (later) j = __ffs(later) - 1;
+            else { j = 32; carry = t_exit; }
+        }
+    }
+    uint32_t samples = visited & occ_mask;
+    uint32_t c = (uint32_t)__popc(samples);
+    const uint32_t room = min(32u - have, budget);
+    bool rewind = false;
+    if (c > room) {                                    // take the first `room` samples only
+        samples &= (1u << __fns(samples, 0, room + 1)) - 1u;
+        c = room;
+        rewind = true;
+    }
+    if (c >= budget) done = true;                      // the ray's max_steps-th sample ends it
+    else if (rewind) done = false;
+    const uint32_t below = samples & ((1u << lane) - 1u);
+    const float prev_next = __shfl_sync(kFull, tn, below ? 31 - __clz(below) : 0);
+    if ((samples >> lane) & 1u) ws.smp[have + __popc(below)] = make_float2(tk, __fsub_rn(tn, below ? prev_next : st.last_t));
+    float next_base = cur;
+    if (samples) {
+        st.last_t = __shfl_sync(kFull, tn, 31 - __clz(samples));
+        if (rewind) { next_base = st.last_t; carry = -FLT_MAX; }   // the candidate after an occupied one is visited next
+    }
+    st.t_base = next_base;
+    st.skip_to = carry;
+    st.done = done;
+    return have + c;
+}
+
 // ---------------------------------------------------------------------------------------------- kernels
 struct DiffArgs {
     const float *rays_o, *rays_d;
@@ -409,7 +488,7 @@ __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs 
         }
         const RayDir rd = make_ray_dir(dx, dy, dz);
         RayAcc acc = {near, 0.f, 0.f, 0.f, 0.f, 0.f};
-        float t = near, last_t = near;
+        MarchState st = {near, near, -FLT_MAX, false};
         uint32_t total = 0;
         bool done = false;
         float4 fin = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -424,17 +503,11 @@ __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs 
         float sh_acc[4] = {0.f, 0.f, 0.f, 0.f};
 
         while (!done) {
-            // march: lane 0 runs the reference's loop body (raymarching.cu:754-812) for up to 32 occupied samples
+            // march: windows of 32 candidate parameters until the chunk holds 32 samples (or the ray ends)
             uint32_t c = 0;
-            if (lane == 0) {
-                while (t < far && c < 32u && total + c < ra.max_steps) {
-                    const float t0 = t;
-                    float x, y, z, dt, dlt;
-                    if (march_probe(m, ox, oy, oz, rd, t, last_t, x, y, z, dt, dlt)) ws.smp[c++] = make_float2(t0, dlt);
-                }
-            }
-            c = __shfl_sync(0xffffffffu, c, 0);
+            while (c < 32u && !st.done) c = march_window(m, ox, oy, oz, rd, far, ra.max_steps - total - c, c, st, ws, lane);
             if (c == 0) break;
+            if (st.done) done = true;       // this chunk is the ray's last
             total += c;
             __syncwarp();
             const bool valid = (uint32_t)lane < c;
@@ -443,7 +516,7 @@ __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs 
             if (valid) {
                 ts = ws.smp[lane].x;
                 x = sample_pos(m, ox, dx, ts); y = sample_pos(m, oy, dy, ts); z = sample_pos(m, oz, dz, ts);
-                encode_point<2>(nc, x, y, z, erow);
+                encode_point<4>(nc, x, y, z, erow);   // 32 loads in flight per trip: latency, not registers, is what this kernel is short of
             } else {
                 erow[0] = erow[1] = erow[2] = erow[3] = make_uint4(0, 0, 0, 0);
             }
@@ -548,7 +621,7 @@ __global__ void __launch_bounds__(kThreads) k_density_backward(NetConst nc, cons
         uint4 *erow = reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride);
         if (valid) {
             x = __ldg(xyzs + 3 * (size_t)i); y = __ldg(xyzs + 3 * (size_t)i + 1); z = __ldg(xyzs + 3 * (size_t)i + 2);
-            encode_point<2>(nc, x, y, z, erow);
+            encode_point<4>(nc, x, y, z, erow);   // 32 loads in flight per trip: latency, not registers, is what this kernel is short of
         } else {
             erow[0] = erow[1] = erow[2] = erow[3] = make_uint4(0, 0, 0, 0);
         }

@@ -77,7 +77,8 @@ class NeRFNetwork(NeRFRenderer):
     def frozen_weights(self):
         """Context manager for render loops over fixed weights (a stress test renders thousands of batches): inside it the fused
         path skips the per-call check that the parameters are still the ones it registered (one 400-byte device-to-host read, a
-        host synchronisation per render call).  The first call inside still registers / verifies."""
+        host synchronisation per render call) and the check that the scene (occupancy bitfield, aabb, min_near) is the one it
+        registered (another small read-back).  The first call inside still registers / verifies both."""
         import contextlib
 
         @contextlib.contextmanager

@@ -216,6 +216,8 @@ class NeRFRenderer(nn.Module):
 
     def _set_scene(self, ctx_owner, handle):
         lib = _cabi.load()
+        if getattr(self, "_frozen", False) and ctx_owner.keys is not None and "scene" in ctx_owner.keys:
+            return   # inside `with model.frozen_weights():` the scene registered by the first call stands (no aabb read-back per call)
         aabb = self.aabb_train if self.training else self.aabb_infer
         bf = self.density_bitfield
         key = (bf.data_ptr(), self.cascade, self.grid_size, tuple(aabb.tolist()), float(self.min_near))

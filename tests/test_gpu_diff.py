@@ -276,3 +276,52 @@ def test_density_gradient_against_the_reference_backward_kernels(world, var, cud
     # measured (B200): A 7.9e-2, B 5.2e-2 (ReLU sign disagreements on a few points + the reference's half dy_dx), C 9.8e-4
     assert e < (5e-3 if var == "C" else 1.5e-1)
     assert med < 2e-2
+
+
+def test_two_cascades_and_cone_stepping(cuda):
+    """bound = 2 (two occupancy cascades, mip levels in the marcher) with dt_gamma > 0 (step size grows with t): the differentiable
+    forward still equals the inference renderer's, and the ray gradients still match the fp64 definition built from the stand-alone
+    marcher's samples."""
+    bitfield, grid = syn.stonehenge_bitfield(cascade=2)
+    w = dict(all_active_weights())
+    w2 = syn.ngp_weights(0, variant="B", bound=2)
+    for k in ("offsets", "per_level_scale", "S", "bound"):
+        w[k] = w2[k]
+    rows = int(w["offsets"][-1])
+    assert rows == w2["table"].shape[0]
+    table = np.abs(w2["table_f32"]).astype(np.float16)
+    w.update(table=table, table_f32=table.astype(np.float32))
+    model = syn.build_model(w, bitfield, grid, device=cuda)
+    assert model.cascade == 2
+    o, d = syn.pinhole_rays(syn.orbit_pose(radius=2.6), 64, 64)
+    pick = np.random.default_rng(4).permutation(o.shape[0])[:256]
+    o = torch.from_numpy(np.ascontiguousarray(o[pick], np.float32)).to(cuda)
+    d = torch.from_numpy(np.ascontiguousarray(d[pick], np.float32)).to(cuda)
+    G = torch.randn(256, 3, generator=torch.Generator().manual_seed(6)).to(cuda)
+    kw = dict(staged=True, bg_color=0.5, perturb=False, dt_gamma=1 / 128, max_steps=MAX_STEPS)
+    with torch.no_grad():
+        ref = model.render(o[None], d[None], **kw)
+    orq, drq = o.clone().requires_grad_(True), d.clone().requires_grad_(True)
+    res = model.render(orq[None], drq[None], **kw)
+    assert float((res["image"] - ref["image"]).abs().max()) < 1e-4
+    assert float((res["weights_sum"] - ref["weights_sum"]).abs().max()) < 1e-4
+    (res["image"][0] * G).sum().backward()
+
+    N = o.shape[0]
+    nears, fars = our_rm.near_far_from_aabb(o, d, model.aabb_infer, model.min_near)
+    alive = torch.arange(N, dtype=torch.int32, device=cuda)
+    _, _, deltas = our_rm.march_rays(N, MAX_STEPS, alive, nears.clone(), o, d, model.bound, model.density_bitfield, model.cascade,
+                                     model.grid_size, nears, fars, -1, False, 1 / 128, MAX_STEPS)
+    t, dt, count = dorc.samples_from_deltas(deltas, nears, N, MAX_STEPS)
+    S = max(int(count.max()), 1)
+    assert int((count > 0).sum()) > N // 4
+    net = dorc.Net(w, device=cuda)
+    od, dd = o.double().requires_grad_(True), d.double().requires_grad_(True)
+    image, _ = dorc.render(net, od, dd, t[:, :S].contiguous(), dt[:, :S].contiguous(), count, bg=0.5)
+    assert float((image.detach() - res["image"][0].double()).abs().max()) < 2e-3
+    (image * G.double()).sum().backward()
+    hit = count > 0
+    mo, md = float(per_row_rel(orq.grad, od.grad)[hit].median()), float(per_row_rel(drq.grad, dd.grad)[hit].median())
+    print(f"bound 2, dt_gamma 1/128: per-ray median error {mo:.3e} / {md:.3e}; aggregate {rel_l2(orq.grad, od.grad):.3e}")
+    assert mo < 1e-2 and md < 1e-2
+    assert rel_l2(orq.grad, od.grad) < 1e-1

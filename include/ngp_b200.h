@@ -215,8 +215,12 @@ int ngp_render_poses_host(ngp_ctx *ctx, const float *poses_host, uint32_t F, uin
  * validate.py:117 falls back to the sampler `run()` whenever gradients w.r.t. rays are wanted.  Here the CUDA-ray render itself is
  * differentiable w.r.t. rays_o / rays_d.  One warp per ray, no workspace: the backward pass re-marches and re-evaluates.
  *
- * forward: the inference result of ngp_render for the same rays (same march / network / compositor functions; a ray takes at most
- * max_steps samples) plus `finals` [N,4] fp32 (16-byte aligned) = raw (r, g, b, weights_sum) per ray, which the backward pass reads. */
+ * forward: the inference render of the same rays with the same march / network / compositor functions as ngp_render, each ray marched
+ * as ONE chunk of at most max_steps samples (the reference restarts its marcher every n_step = clamp(N / n_alive, 1, 8) samples from
+ * a re-summed t, raymarching.cu:723-725,870,905; after a large empty gap that t can be one ulp off, so a few rays in 10^5 take one
+ * sample more or fewer there than here), plus `finals` [N,4] fp32 (16-byte aligned) = raw (r, g, b, weights_sum) per ray, which
+ * the backward pass reads.  Also the faster renderer for small inference batches (no cooperative launch, no workspace): see
+ * NeRFRenderer.small_batch_rays. */
 int ngp_render_diff_forward(ngp_ctx *ctx, const float *rays_o, const float *rays_d, uint32_t N, float dt_gamma,
                             uint32_t max_steps, float bg_color, float *image, float *depth, float *weights_sum,
                             float *finals, int32_t *samples_per_ray, void *stream);

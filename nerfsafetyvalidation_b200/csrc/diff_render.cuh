@@ -112,6 +112,8 @@ __device__ __forceinline__ void load_frags32(const __half *s_rows, int stride, i
 
 // One net of network_ff.py:26-49 on this warp's 32 rows: [32] -> 64 -> (nh x 64) -> 16 output columns (O holds columns 0..15).
 // masks[0] <- first layer's ReLU, masks[1 + k] <- hidden matmul k's.
+// (inlined on purpose: a non-inlined copy shared by both nets halves the code but passes the fragments through local memory, which
+// costs the warp-per-ray kernel 1.6x of its throughput at 16 000+ rays)
 __device__ __forceinline__ void net_forward(const uint2 *__restrict__ w_first, const uint2 *__restrict__ w_hidden, const uint2 *__restrict__ w_last,
                                             uint32_t nh, const uint32_t (&A0)[2][2][4], int lane, float (&O)[2][2][4], uint64_t (&masks)[kMaxHidden]) {
     float C[2][8][4];
@@ -210,6 +212,7 @@ __device__ __forceinline__ void sh_basis_grad(float x, float y, float z, const f
 
 // d(sum_j denc[j] * enc_j(x, y, z)) / d(x, y, z): the trilinear interpolation's input gradient (gridencoder.cu:180-223), fp32,
 // corners re-gathered (they are L2-resident: the forward of the same chunk has just read them).  denc: 32 floats, column 2 l + c.
+template <bool kGeneral>
 __device__ __forceinline__ void grid_input_grad(const NetConst &nc, float x, float y, float z, const float *denc, float &gx, float &gy, float &gz) {
     gx = gy = gz = 0.0f;
     float u0, u1, u2;
@@ -222,7 +225,7 @@ __device__ __forceinline__ void grid_input_grad(const NetConst &nc, float x, flo
         const uint32_t g0 = (uint32_t)floorf(p0), g1 = (uint32_t)floorf(p1), g2 = (uint32_t)floorf(p2);
         const float f0 = p0 - (float)g0, f1 = p1 - (float)g1, f2 = p2 - (float)g2;
         uint32_t row[8];
-        cell_rows<true>(lc, g0, g1, g2, row);
+        cell_rows<kGeneral>(lc, g0, g1, g2, row);
         float2 v[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = __half22float2(__ldg(nc.lvbase[l] + row[k]));
@@ -458,7 +461,7 @@ struct DiffArgs {
     float *g_o, *g_d;          // [N,3]
 };
 
-template <bool kBackward>
+template <bool kBackward, bool kGeneral>
 __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs ra) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint2 *s_w = reinterpret_cast<uint2 *>(smem_raw);
@@ -516,7 +519,7 @@ __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs 
             if (valid) {
                 ts = ws.smp[lane].x;
                 x = sample_pos(m, ox, dx, ts); y = sample_pos(m, oy, dy, ts); z = sample_pos(m, oz, dz, ts);
-                encode_point<4>(nc, x, y, z, erow);   // 32 loads in flight per trip: latency, not registers, is what this kernel is short of
+                encode_point<4, kGeneral>(nc, x, y, z, erow);   // 32 loads in flight per trip: latency, not registers, is what this kernel is short of
             } else {
                 erow[0] = erow[1] = erow[2] = erow[3] = make_uint4(0, 0, 0, 0);
             }
@@ -552,7 +555,7 @@ __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs 
                 __syncwarp();
                 if (used) {
                     float gx, gy, gz;
-                    grid_input_grad(nc, x, y, z, ws.denc + lane * kDencStride, gx, gy, gz);
+                    grid_input_grad<kGeneral>(nc, x, y, z, ws.denc + lane * kDencStride, gx, gy, gz);
                     // x = clamp(o + t d, -bound, bound) (raymarching.cu:756-758): no gradient through a clamped coordinate
                     if (fabsf(__fmaf_rn(dx, ts, ox)) > m.bound) gx = 0.f;
                     if (fabsf(__fmaf_rn(dy, ts, oy)) > m.bound) gy = 0.f;
@@ -598,6 +601,7 @@ __global__ void __launch_bounds__(kThreads) k_diff_render(NetConst nc, DiffArgs 
 }
 
 // d loss / d xyz of sigma = exp(h0) (* density_scale) for M points (network_ff.py:76-89): one warp per 32 points.
+template <bool kGeneral>
 __global__ void __launch_bounds__(kThreads) k_density_backward(NetConst nc, const uint2 *__restrict__ wpack_t, const float *__restrict__ xyzs,
                                                               const float *__restrict__ g_sigma, uint32_t M, float *__restrict__ g_xyz) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -621,7 +625,7 @@ __global__ void __launch_bounds__(kThreads) k_density_backward(NetConst nc, cons
         uint4 *erow = reinterpret_cast<uint4 *>(ws.enc + lane * kEncStride);
         if (valid) {
             x = __ldg(xyzs + 3 * (size_t)i); y = __ldg(xyzs + 3 * (size_t)i + 1); z = __ldg(xyzs + 3 * (size_t)i + 2);
-            encode_point<4>(nc, x, y, z, erow);   // 32 loads in flight per trip: latency, not registers, is what this kernel is short of
+            encode_point<4, kGeneral>(nc, x, y, z, erow);   // 32 loads in flight per trip: latency, not registers, is what this kernel is short of
         } else {
             erow[0] = erow[1] = erow[2] = erow[3] = make_uint4(0, 0, 0, 0);
         }
@@ -635,7 +639,7 @@ __global__ void __launch_bounds__(kThreads) k_density_backward(NetConst nc, cons
         __syncwarp();
         if (valid) {
             float gx, gy, gz;
-            grid_input_grad(nc, x, y, z, ws.denc + lane * kDencStride, gx, gy, gz);
+            grid_input_grad<kGeneral>(nc, x, y, z, ws.denc + lane * kDencStride, gx, gy, gz);
             g_xyz[3 * (size_t)i] = gx; g_xyz[3 * (size_t)i + 1] = gy; g_xyz[3 * (size_t)i + 2] = gz;
         }
         __syncwarp();

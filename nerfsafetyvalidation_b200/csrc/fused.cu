@@ -127,7 +127,7 @@ __device__ __forceinline__ void encode_trip(const NetConst &nc, float u0, float 
 }
 
 // 16-level hash-grid encoding of one point into 16 half2: dst[g * stride], g = 0..3, receives levels 4g .. 4g+3 (8 halves).
-template <int kLevelsPerTrip = 4>
+template <int kLevelsPerTrip = 4, bool kGeneral = true>
 __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float y, float z, uint4 *dst, int stride = 1) {
     static_assert(kLevelsPerTrip == 4 || kLevelsPerTrip == 2 || kLevelsPerTrip == 1, "a trip covers a whole, a half or a quarter of a 16-byte operand chunk");
     float u0, u1, u2;
@@ -140,7 +140,7 @@ __device__ __forceinline__ void encode_point(const NetConst &nc, float x, float 
 #pragma unroll 1
     for (int trip = 0; trip < 16 / kLevelsPerTrip; trip++) {
         uint32_t packed[kLevelsPerTrip];
-        encode_trip<kLevelsPerTrip>(nc, u0, u1, u2, trip, packed);
+        encode_trip<kLevelsPerTrip, kGeneral>(nc, u0, u1, u2, trip, packed);
         if (kLevelsPerTrip == 4) dst[trip * stride] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
         else if (kLevelsPerTrip == 2) reinterpret_cast<uint2 *>(dst + (trip >> 1) * stride)[trip & 1] = make_uint2(packed[0], packed[kLevelsPerTrip - 1]);
         else reinterpret_cast<uint32_t *>(dst + (trip >> 2) * stride)[trip & 3] = packed[0];
@@ -1443,9 +1443,12 @@ int ngp_ctx_set_network(ngp_ctx *c, const void *table_f16, const int32_t *offset
         if (int rc = after_launch("pack_network_transposed")) return rc;
         for (int b = 0; b < 2; b++) c->diff_smem[b] = (size_t)count * 8 * (b + 1) + diff::kWarps * diff::warp_smem_bytes(b != 0);
         NGP_REQUIRE(c->diff_smem[1] <= c->max_smem_optin, "differentiable render: %zu B of shared memory do not fit an SM", c->diff_smem[1]);
-        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[0]));
-        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
-        NGP_CUDA(cudaFuncSetAttribute(diff::k_density_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[0]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[0]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_diff_render<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_density_backward<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
+        NGP_CUDA(cudaFuncSetAttribute(diff::k_density_backward<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->diff_smem[1]));
     }
     {
         const tc::WeightMap wm = tc::weight_map(nc.nh_sigma, nc.nh_color);
@@ -1594,7 +1597,10 @@ int ngp_render_diff_forward(ngp_ctx *c, const float *rays_o, const float *rays_d
     if (samples_per_ray) NGP_DEVPTR(samples_per_ray);
     da.image = image; da.depth = depth; da.weights_sum = weights_sum; da.finals = reinterpret_cast<float4 *>(finals);
     da.samples_per_ray = samples_per_ray;
-    diff::k_diff_render<false><<<diff_grid(c, N), diff::kThreads, c->diff_smem[0], as_stream(stream)>>>(c->nc, da);
+    // kGeneral = false: every level is a dense grid that fits its table or a power-of-two hash table (every NGP configuration); the
+    // general instantiation carries the integer-division index paths as well
+    if (c->fast_levels) diff::k_diff_render<false, false><<<diff_grid(c, N), diff::kThreads, c->diff_smem[0], as_stream(stream)>>>(c->nc, da);
+    else diff::k_diff_render<false, true><<<diff_grid(c, N), diff::kThreads, c->diff_smem[0], as_stream(stream)>>>(c->nc, da);
     return after_launch("render_diff_forward");
 }
 
@@ -1609,7 +1615,8 @@ int ngp_render_diff_backward(ngp_ctx *c, const float *rays_o, const float *rays_
     if (grad_weights_sum) NGP_DEVPTR(grad_weights_sum);
     da.finals = const_cast<float4 *>(reinterpret_cast<const float4 *>(finals));
     da.g_image = grad_image; da.g_ws = grad_weights_sum; da.g_o = grad_rays_o; da.g_d = grad_rays_d;
-    diff::k_diff_render<true><<<diff_grid(c, N), diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(c->nc, da);
+    if (c->fast_levels) diff::k_diff_render<true, false><<<diff_grid(c, N), diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(c->nc, da);
+    else diff::k_diff_render<true, true><<<diff_grid(c, N), diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(c->nc, da);
     return after_launch("render_diff_backward");
 }
 
@@ -1620,8 +1627,9 @@ int ngp_density_backward(ngp_ctx *c, const float *xyzs, const float *grad_sigmas
     NGP_DEVPTR(xyzs); NGP_DEVPTR(grad_sigmas); NGP_DEVPTR(grad_xyzs);
     NetConst nc = c->nc;
     if (!apply_density_scale) nc.density_scale = 1.0f;
-    diff::k_density_backward<<<diff_grid(c, div_up(M, 32u)), diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(nc, c->wpack_t, xyzs, grad_sigmas,
-                                                                                                                   M, grad_xyzs);
+    const uint32_t blocks = diff_grid(c, div_up(M, 32u));
+    if (c->fast_levels) diff::k_density_backward<false><<<blocks, diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(nc, c->wpack_t, xyzs, grad_sigmas, M, grad_xyzs);
+    else diff::k_density_backward<true><<<blocks, diff::kThreads, c->diff_smem[1], as_stream(stream)>>>(nc, c->wpack_t, xyzs, grad_sigmas, M, grad_xyzs);
     return after_launch("density_backward");
 }
 

@@ -108,6 +108,14 @@ class NeRFRenderer(nn.Module):
             self.local_step = 0
         self._native = _NativeCtx()
         self.fused = True   # run_cuda default mode
+        # Opt-in: inference batches of at most this many rays go to the warp-per-ray kernel (ngp_render_diff_forward) instead of the
+        # persistent one, whose fixed cost (a cooperative launch, two grid barriers per epoch) dominates small batches: 1024 rays
+        # 0.13 ms instead of 1.5 ms, break-even around 40 000 rays (profiles/r02i_small_batch.json).  Off by default because the two
+        # differ where the reference itself depends on the batch: its marcher restarts every chunk of n_step = clamp(N // n_alive, 1, 8)
+        # samples from a re-summed t (raymarching.cu:723-725, 870, 905), which after a large empty gap can be one ulp off and move one
+        # sample across a cell face.  The persistent kernel reproduces that schedule exactly; the warp-per-ray kernel marches each ray
+        # as ONE chunk (measured: 2 of 65 536 rays take one sample more / fewer, image difference 1.4e-3 on those, <= 1e-6 elsewhere).
+        self.small_batch_rays = 0
 
     def forward(self, x, d):
         raise NotImplementedError()
@@ -253,10 +261,28 @@ class NeRFRenderer(nn.Module):
             from .autograd import RenderRays
             image, depth, weights_sum = RenderRays.apply(rays_o, rays_d, self, float(dt_gamma), int(max_steps), float(bg_color))
             return {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum, "sigmas": None, "rgbs": None}
+        if (fused and 0 < N <= int(self.small_batch_rays) and not perturb and scalar_bg and not return_stats and not return_uq
+                and self._configure_native(self._native)):
+            return self._run_warp_per_ray(rays_o, rays_d, prefix, N, device, float(dt_gamma), int(max_steps), float(bg_color))
         if fused and not perturb and scalar_bg and self._configure_native(self._native):
             return self._run_fused(rays_o, rays_d, prefix, N, device, float(dt_gamma), int(max_steps), float(bg_color), return_stats,
                                    return_uq)
         return self._run_stepwise(rays_o, rays_d, prefix, N, device, dt_gamma, bg_color, perturb, max_steps)
+
+    def _run_warp_per_ray(self, rays_o, rays_d, prefix, N, device, dt_gamma, max_steps, bg_color):
+        """Small inference batches on the warp-per-ray kernel (see `small_batch_rays`): one launch, no workspace."""
+        lib = _cabi.load()
+        image = torch.empty(N, 3, dtype=torch.float32, device=device)
+        depth = torch.empty(N, dtype=torch.float32, device=device)
+        weights_sum = torch.empty(N, dtype=torch.float32, device=device)
+        finals = torch.empty(N, 4, dtype=torch.float32, device=device)
+        with torch.cuda.device(device):
+            handle = self._native.get(device)
+            self._set_scene(self._native, handle)
+            _cabi.check(lib.ngp_render_diff_forward(handle, _cabi.ptr(rays_o), _cabi.ptr(rays_d), N, dt_gamma, max_steps, bg_color,
+                                                    _cabi.ptr(image), _cabi.ptr(depth), _cabi.ptr(weights_sum), _cabi.ptr(finals), None,
+                                                    _cabi.stream()), "ngp_render_diff_forward")
+        return {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum, "sigmas": None, "rgbs": None}
 
     def _run_fused(self, rays_o, rays_d, prefix, N, device, dt_gamma, max_steps, bg_color, return_stats, return_uq=False):
         lib = _cabi.load()

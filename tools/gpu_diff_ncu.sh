@@ -8,3 +8,4 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
     python tools/diff_bench.py --iters 3 --warmup 1 > gpurun_out/ncu_diff_launches.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_diff_render|k_density_backward' -c 3 -s 6 -o gpurun_out/prof_${TAG}_diff -f \
     python tools/diff_bench.py --iters 3 --warmup 1 > gpurun_out/ncu_diff_full.log 2>&1; tail -3 gpurun_out/ncu_diff_full.log
+timeout 300 python tools/small_batch_probe.py > gpurun_out/${TAG}_small_batch.json 2> gpurun_out/small_batch.err

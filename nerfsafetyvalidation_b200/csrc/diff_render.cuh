@@ -2,6 +2,8 @@
 // mma.sync building blocks): what Estimator.measurement_fn (nav/estimator_helpers.py:191-225, <= 1024 rays, loss.backward() on the
 // pose) and the planner's density queries (nav/quad_plot.py:223-300 through validate.py:288) need from the CUDA-ray path.
 //
+//   (second template argument of every kernel: kGeneral = the hash grid has levels that need the integer-division index paths;
+//    false for every NGP table, which keeps those paths out of the instruction stream)
 //   k_diff_render<false>   forward: one WARP per ray -- march (32 candidate parameters per step, see march_window) -> 32-sample chunks -> hash grid ->
 //                          both MLPs (mma.sync, fp32 accumulate) -> front-to-back compositing with the T < 1e-4 stop.  Same functions
 //                          as the inference renderer, sample for sample.

@@ -357,3 +357,35 @@ def test_two_cascades_and_cone_stepping(cuda):
     print(f"bound 2, dt_gamma 1/128: per-ray median error {mo:.3e} / {md:.3e}; aggregate {rel_l2(orq.grad, od.grad):.3e}")
     assert mo < 1e-2 and md < 1e-2
     assert rel_l2(orq.grad, od.grad) < 1e-1
+
+
+@pytest.mark.parametrize("nl,nlc", [(3, 2), (4, 4)])
+def test_other_network_depths(cuda, scene, nl, nlc):
+    """num_layers / num_layers_color other than the default (2, 3): the rolled hidden-layer loops and the mask bookkeeping."""
+    bitfield, grid = scene
+    w = syn.ngp_weights(0, variant="B", num_layers=nl, num_layers_color=nlc)
+    model = syn.build_model(w, bitfield, grid, device=cuda)
+    o, d = syn.pinhole_rays(syn.orbit_pose(), 64, 64)
+    pick = np.random.default_rng(2).permutation(o.shape[0])[:128]
+    o = torch.from_numpy(np.ascontiguousarray(o[pick], np.float32)).to(cuda)
+    d = torch.from_numpy(np.ascontiguousarray(d[pick], np.float32)).to(cuda)
+    G = torch.randn(128, 3, generator=torch.Generator().manual_seed(1)).to(cuda)
+    with torch.no_grad():
+        ref = model.render(o[None], d[None], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
+    res, go, gd = our_grads(model, o, d, G)
+    assert_same_render(res, ref)
+    t, dt, count = marched_samples(model, o, d)
+    net = dorc.Net(w, device=cuda)
+    od, dd = o.double().requires_grad_(True), d.double().requires_grad_(True)
+    image, _ = dorc.render(net, od, dd, t, dt, count, bg=1.0)
+    (image * G.double()).sum().backward()
+    hit = count > 0
+    mo, md = float(per_row_rel(go, od.grad)[hit].median()), float(per_row_rel(gd, dd.grad)[hit].median())
+    print(f"layers {nl}/{nlc}: per-ray median error {mo:.3e} / {md:.3e}; aggregate {rel_l2(go, od.grad):.3e}")
+    assert mo < 3e-2 and md < 3e-2 and rel_l2(go, od.grad) < 1.5e-1
+    x = (torch.rand(2048, 3, generator=torch.Generator().manual_seed(5)) * 2 - 1).to(cuda)
+    xr = x.clone().requires_grad_(True)
+    model.density(xr)["sigma"].sum().backward()
+    xd = x.double().requires_grad_(True)
+    net.density(xd)[0].sum().backward()
+    assert float(per_row_rel(xr.grad, xd.grad).median()) < 5e-3

@@ -389,3 +389,32 @@ def test_other_network_depths(cuda, scene, nl, nlc):
     xd = x.double().requires_grad_(True)
     net.density(xd)[0].sum().backward()
     assert float(per_row_rel(xr.grad, xd.grad).median()) < 5e-3
+
+
+def test_sample_budget(world, cuda):
+    """max_steps = 6 (the step size is then dt_max = 2 sqrt(3) / 128, raymarching.cu:745-746): many rays run out of their sample budget
+    inside the occupied region.  The warp-per-ray kernels give a ray exactly
+    max_steps samples (the reference's loop, `while step < max_steps` over chunks of n_step, gives between max_steps and max_steps + 7
+    depending on the batch), which is what the stand-alone marcher does with one chunk of n_step = max_steps."""
+    model, w, o, d, G = world["mC"], world["wC"], world["o"], world["d"], world["G"]
+    steps = 6
+    orq, drq = o.clone().requires_grad_(True), d.clone().requires_grad_(True)
+    res = model.render(orq[None], drq[None], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=steps)
+    (res["image"][0] * G).sum().backward()
+    N = o.shape[0]
+    nears, fars = our_rm.near_far_from_aabb(o, d, model.aabb_infer, model.min_near)
+    alive = torch.arange(N, dtype=torch.int32, device=cuda)
+    _, _, deltas = our_rm.march_rays(N, steps, alive, nears.clone(), o, d, model.bound, model.density_bitfield, model.cascade,
+                                     model.grid_size, nears, fars, -1, False, 0, steps)
+    t, dt, count = dorc.samples_from_deltas(deltas, nears, N, steps)
+    assert int((count == steps).sum()) > N // 8, "the budget should bind for many rays"
+    net = dorc.Net(w, device=cuda)
+    od, dd = o.double().requires_grad_(True), d.double().requires_grad_(True)
+    image, ws = dorc.render(net, od, dd, t, dt, count, bg=1.0)
+    assert float((image.detach() - res["image"][0].double()).abs().max()) < 2e-3
+    assert float((ws.detach() - res["weights_sum"].double()).abs().max()) < 2e-3
+    (image * G.double()).sum().backward()
+    hit = count > 0
+    mo = float(per_row_rel(orq.grad, od.grad)[hit].median())
+    print(f"max_steps {steps}: per-ray median error {mo:.3e}, aggregate {rel_l2(orq.grad, od.grad):.3e}")
+    assert mo < 5e-3 and rel_l2(orq.grad, od.grad) < 5e-2

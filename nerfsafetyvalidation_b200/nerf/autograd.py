@@ -95,3 +95,38 @@ class DensityPoints(torch.autograd.Function):
             _cabi.check(lib.ngp_density_backward(model._native.get(device), _cabi.ptr(x), _cabi.ptr(g_sigma), M, 0, _cabi.ptr(g_x),
                                                  _cabi.stream()), "ngp_density_backward")
         return g_x, None
+
+
+class GetRays(torch.autograd.Function):
+    """rays_o, rays_d [B,H*W,3] = GetRays.apply(poses [B,4,4], fx, fy, cx, cy, H, W): nerf/utils.py:52-116 (N <= 0) with the gradient
+    w.r.t. the poses that the reference's torch sequence carries -- what Estimator.measurement_fn differentiates through
+    (nav/estimator_helpers.py:203-210).  Forward: one kernel (ngp_get_rays).  Backward (two tiny reductions, left to torch):
+    rays_o = t (broadcast) -> d t = sum over pixels of g_o;  rays_d = R dir_cam -> d R = sum over pixels of g_d (x) dir_cam."""
+
+    @staticmethod
+    def forward(ctx, poses, fx, fy, cx, cy, H, W):
+        lib = _cabi.load()
+        poses = poses.detach().to(torch.float32).contiguous()
+        B = poses.shape[0]
+        rays_o = torch.empty(B, H * W, 3, dtype=torch.float32, device=poses.device)
+        rays_d = torch.empty(B, H * W, 3, dtype=torch.float32, device=poses.device)
+        with torch.cuda.device(poses.device):
+            _cabi.check(lib.ngp_get_rays(_cabi.ptr(poses), B, H, W, fx, fy, cx, cy, _cabi.ptr(rays_o), _cabi.ptr(rays_d), _cabi.stream()),
+                        "ngp_get_rays")
+        ctx.args = (fx, fy, cx, cy, H, W, poses.device)
+        return rays_o, rays_d
+
+    @staticmethod
+    def backward(ctx, g_o, g_d):
+        fx, fy, cx, cy, H, W, device = ctx.args
+        B = (g_o if g_o is not None else g_d).shape[0]
+        g_pose = torch.zeros(B, 4, 4, dtype=torch.float32, device=device)
+        if g_o is not None:
+            g_pose[:, :3, 3] = g_o.sum(1)
+        if g_d is not None:
+            j, i = torch.meshgrid(torch.arange(H, device=device, dtype=torch.float32) + 0.5,
+                                  torch.arange(W, device=device, dtype=torch.float32) + 0.5, indexing="ij")
+            dirs = torch.stack(((i - cx) / fx, (j - cy) / fy, torch.ones_like(i)), -1).reshape(H * W, 3)
+            dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+            g_pose[:, :3, :3] = torch.einsum("bpk,pc->bkc", g_d.float(), dirs)      # rays_d[b,p,k] = sum_c R[b,k,c] dirs[p,c]
+        return g_pose, None, None, None, None, None, None

@@ -9,15 +9,22 @@ def custom_meshgrid(*args):
     return torch.meshgrid(*args, indexing="ij")
 
 
-@torch.no_grad()
 def get_rays(poses, intrinsics, H, W, N=-1, error_map=None):
     """nerf/utils.py:52-116 for the inference case (N <= 0: every pixel, pixel centres at +0.5).
     poses [B,4,4] cam2world (CUDA), intrinsics (fx, fy, cx, cy) -> dict(rays_o [B,H*W,3], rays_d [B,H*W,3]).
-    One kernel (ngp_get_rays) instead of the reference's meshgrid / stack / norm / matmul sequence; no CPU fallback."""
+    One kernel (ngp_get_rays) instead of the reference's meshgrid / stack / norm / matmul sequence; no CPU fallback.  Poses that
+    require grad keep their graph (nerf/autograd.py:GetRays), as they do through the reference's torch sequence."""
     if N > 0:
         raise NotImplementedError("get_rays: random pixel sub-sampling (N > 0) is the training path")
     _cabi.require_cuda(poses)
     fx, fy, cx, cy = (float(v) for v in intrinsics)
+    if torch.is_grad_enabled() and poses.requires_grad:
+        # the estimator differentiates its loss w.r.t. the pose through this call (nav/estimator_helpers.py:203-210)
+        from .autograd import GetRays
+        if tuple(poses.shape[1:]) != (4, 4):
+            raise RuntimeError(f"get_rays: poses must be [B,4,4], got {tuple(poses.shape)}")
+        rays_o, rays_d = GetRays.apply(poses, fx, fy, cx, cy, int(H), int(W))
+        return {"rays_o": rays_o, "rays_d": rays_d}
     poses = poses.detach().to(torch.float32).contiguous()
     B = poses.shape[0]
     if tuple(poses.shape[1:]) != (4, 4):

@@ -418,3 +418,45 @@ def test_sample_budget(world, cuda):
     mo = float(per_row_rel(orq.grad, od.grad)[hit].median())
     print(f"max_steps {steps}: per-ray median error {mo:.3e}, aggregate {rel_l2(orq.grad, od.grad):.3e}")
     assert mo < 5e-3 and rel_l2(orq.grad, od.grad) < 5e-2
+
+
+def reference_get_rays(poses, intrinsics, H, W):
+    """nerf/utils.py:52-116 with N = -1, restated in torch (differentiable w.r.t. the poses, as the reference's is)."""
+    fx, fy, cx, cy = intrinsics
+    device = poses.device
+    i, j = torch.meshgrid(torch.linspace(0, W - 1, W, device=device), torch.linspace(0, H - 1, H, device=device), indexing="ij")
+    i = i.t().reshape(1, H * W) + 0.5
+    j = j.t().reshape(1, H * W) + 0.5
+    zs = torch.ones_like(i)
+    directions = torch.stack(((i - cx) / fx * zs, (j - cy) / fy * zs, zs), dim=-1)
+    directions = directions / torch.norm(directions, dim=-1, keepdim=True)
+    rays_d = directions @ poses[:, :3, :3].transpose(-1, -2)
+    rays_o = poses[..., :3, 3][..., None, :].expand_as(rays_d)
+    return rays_o, rays_d
+
+
+def test_pose_gradient_through_get_rays_and_render(world, cuda):
+    """Estimator.measurement_fn's chain (nav/estimator_helpers.py:203-218): pose -> get_rays -> pixel batch -> render_fn -> loss.backward().
+    get_rays carries the pose gradient like the reference's torch version; the whole chain's d loss / d pose equals the one obtained
+    with the torch restatement of get_rays in front of the same renderer."""
+    from nerfsafetyvalidation_b200.nerf.utils import get_rays
+    model = world["mB"]
+    H = W = 40
+    intr = (55.0, 55.0, W / 2, H / 2)
+    pose0 = torch.from_numpy(syn.orbit_pose()[None].astype(np.float32)).to(cuda)
+    batch = torch.from_numpy(np.random.default_rng(1).permutation(H * W)[:512]).to(cuda)
+    target = torch.rand(512, 3, generator=torch.Generator().manual_seed(2)).to(cuda)
+    grads, images = [], []
+    for rays_fn in (lambda p: tuple(get_rays(p, intr, H, W)[k] for k in ("rays_o", "rays_d")), lambda p: reference_get_rays(p, intr, H, W)):
+        pose = pose0.clone().requires_grad_(True)
+        ro, rd = rays_fn(pose)
+        assert ro.requires_grad and rd.requires_grad
+        out = model.render(ro[:, batch], rd[:, batch], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
+        loss = torch.nn.functional.mse_loss(out["image"].reshape(-1, 3), target)
+        loss.backward()
+        grads.append(pose.grad.clone())
+        images.append(out["image"].detach())
+    assert float(grads[0][:, :3].abs().max()) > 0 and float(grads[0][:, 3].abs().max()) == 0
+    assert float((images[0] - images[1]).abs().max()) < 1e-4
+    # the rays of the two versions agree to ~2e-7 (test_gpu_parity.py), so the renderer sees nearly the same inputs
+    assert rel_l2(grads[0], grads[1]) < 2e-2, (grads[0], grads[1])

@@ -460,3 +460,81 @@ def test_pose_gradient_through_get_rays_and_render(world, cuda):
     assert float((images[0] - images[1]).abs().max()) < 1e-4
     # the rays of the two versions agree to ~2e-7 (test_gpu_parity.py), so the renderer sees nearly the same inputs
     assert rel_l2(grads[0], grads[1]) < 2e-2, (grads[0], grads[1])
+
+
+def blob_scene_weights():
+    """A hand-built NGP network that behaves like a TRAINED scene where it matters for pose refinement: a smooth density blob that has
+    faded to ~1 % of its peak where the occupancy grid cuts it off, smooth colour, nothing at the scale of the fine hash levels.
+    Level 0 (dense 17^3 grid) carries f0 = exp(-|p|^2 / (2 * 0.35^2)) and f1 = 0.5 + 0.5 sin(3x) cos(2y); level 1 is the constant 1 (the
+    networks have no biases); every other level is zero.  sigma = exp(12 f0 - 8), rgb = sigmoid((4 f1 - 2, 2 - 4 f1, 0.5))."""
+    w = dict(syn.ngp_weights(0, variant="A"))
+    table = np.zeros_like(w["table_f32"])
+    off = np.asarray(w["offsets"], np.int64)
+    i = np.arange(17, dtype=np.float64)
+    p = ((i - 0.5) / 15.0) * 2 - 1                                  # world coordinate of level-0 grid node i (pos = u * 15 + 0.5)
+    Z, Y, X = np.meshgrid(p, p, p, indexing="ij")                   # row = x + 17 y + 289 z
+    f0 = np.exp(-(X * X + Y * Y + Z * Z) / (2 * 0.35 ** 2))
+    f1 = 0.5 + 0.5 * np.sin(3 * X) * np.cos(2 * Y)
+    table[off[0]:off[0] + 17 ** 3, 0] = f0.reshape(-1)
+    table[off[0]:off[0] + 17 ** 3, 1] = f1.reshape(-1)
+    table[off[1]:off[2], 0] = 1.0
+    ws = np.zeros(64 * (32 + 64 + 16), np.float32)
+    W0, W1, W2 = ws[:2048].reshape(64, 32), ws[2048:2048 + 4096].reshape(64, 64), ws[2048 + 4096:].reshape(16, 64)
+    W0[0, 0] = W0[1, 1] = W0[2, 2] = 1.0                            # hidden units 0, 1, 2 <- f0, f1, 1
+    W1[0, 0] = W1[1, 1] = W1[2, 2] = 1.0
+    W2[0, 0], W2[0, 2] = 12.0, -8.0                                 # log-density
+    W2[1, 1] = 1.0                                                  # geo_feat[0] = f1
+    W2[2, 2] = 1.0                                                  # geo_feat[1] = 1
+    wc = np.zeros(64 * (32 + 2 * 64 + 16), np.float32)
+    C0, C1, C2, C3 = (wc[:2048].reshape(64, 32), wc[2048:2048 + 4096].reshape(64, 64), wc[2048 + 4096:2048 + 8192].reshape(64, 64),
+                      wc[2048 + 8192:].reshape(16, 64))
+    C0[0, 16] = C0[1, 17] = 1.0                                     # colour input columns 16, 17 = geo_feat[0], geo_feat[1]
+    C1[0, 0] = C1[1, 1] = C2[0, 0] = C2[1, 1] = 1.0
+    C3[0, 0], C3[0, 1] = 4.0, -2.0
+    C3[1, 0], C3[1, 1] = -4.0, 2.0
+    C3[2, 1] = 0.5
+    t16, ws16, wc16 = table.astype(np.float16), ws.astype(np.float16), wc.astype(np.float16)
+    w.update(table=t16, table_f32=t16.astype(np.float32), w_sigma=ws16, w_sigma_f32=ws16.astype(np.float32), w_color=wc16,
+             w_color_f32=wc16.astype(np.float32), density_scale=1.0)
+    return w
+
+
+def test_pose_refinement_on_a_smooth_scene(cuda):
+    """The estimator's loop in miniature (nav/estimator_helpers.py:120-160): the observation is the render at the true pose, the state
+    starts 3 cm off, Adam follows d loss / d pose through get_rays and the differentiable render.  The occupancy grid is derived from
+    the network itself by update_extra_state (renderer.py:451-546).  The loss and the pose error both shrink."""
+    from nerfsafetyvalidation_b200.nerf.utils import get_rays
+    w = blob_scene_weights()
+    model = syn.build_model(w, None, None, device=cuda)
+    torch.manual_seed(0)
+    model.update_extra_state()
+    occupied = int((model.density_grid > min(model.mean_density, model.density_thresh)).sum())
+    assert 1000 < occupied < 128 ** 3 // 4, occupied
+    H = W = 48
+    intr = (60.0, 60.0, W / 2, H / 2)
+    true_pose = torch.from_numpy(syn.orbit_pose()[None].astype(np.float32)).to(cuda)
+    kw = dict(staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
+    with torch.no_grad():
+        r = get_rays(true_pose, intr, H, W)
+        target = model.render(r["rays_o"], r["rays_d"], **kw)["image"][0]
+    assert float(target.std()) > 0.02, "the blob should be visible"
+    batch = torch.from_numpy(np.random.default_rng(3).permutation(H * W)[:1024]).to(cuda)
+    delta0 = torch.tensor([0.02, -0.015, 0.015], device=cuda)
+    delta = delta0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([delta], lr=1e-3)
+    losses = []
+    with model.frozen_weights():
+        for _ in range(80):
+            pose = true_pose.clone()
+            pose[:, :3, 3] = true_pose[:, :3, 3] + delta
+            rays = get_rays(pose, intr, H, W)
+            out = model.render(rays["rays_o"][:, batch], rays["rays_d"][:, batch], **kw)
+            loss = torch.nn.functional.mse_loss(out["image"][0], target[batch])
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(float(loss))
+    err0, err1 = float(delta0.norm()), float(delta.detach().norm())
+    print(f"pose refinement: loss {losses[0]:.3e} -> {losses[-1]:.3e}, translation error {err0:.4f} -> {err1:.4f}")
+    assert losses[-1] < 0.25 * losses[0]
+    assert err1 < 0.5 * err0

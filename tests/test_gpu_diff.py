@@ -538,3 +538,26 @@ def test_pose_refinement_on_a_smooth_scene(cuda):
     print(f"pose refinement: loss {losses[0]:.3e} -> {losses[-1]:.3e}, translation error {err0:.4f} -> {err1:.4f}")
     assert losses[-1] < 0.25 * losses[0]
     assert err1 < 0.5 * err0
+
+
+def test_density_descent_on_a_smooth_scene(cuda):
+    """The planner's use of density_fn under autograd (nav/quad_plot.py:223-300: way-points are pushed out of dense regions by gradient
+    descent on a collision cost): on the blob scene, descending sum(sigma) moves every point away from the blob's centre."""
+    model = syn.build_model(blob_scene_weights(), None, None, device=cuda)
+    g = torch.Generator().manual_seed(4)
+    dirs = torch.randn(256, 3, generator=g)
+    x0 = (dirs / dirs.norm(dim=-1, keepdim=True) * (0.15 + 0.2 * torch.rand(256, 1, generator=g))).to(cuda)
+    x = x0.clone().requires_grad_(True)
+    opt = torch.optim.SGD([x], lr=1e-3)
+    with model.frozen_weights():
+        first = None
+        for _ in range(30):
+            cost = model.density(x)["sigma"].sum()
+            first = float(cost) if first is None else first
+            opt.zero_grad()
+            cost.backward()
+            opt.step()
+    last = float(model.density(x.detach())["sigma"].sum())
+    moved_out = (x.detach().norm(dim=-1) > x0.norm(dim=-1)).float().mean()
+    print(f"density descent: cost {first:.3e} -> {last:.3e}, {float(moved_out) * 100:.0f} % of the points moved outwards")
+    assert last < 0.7 * first and float(moved_out) > 0.95

@@ -561,3 +561,31 @@ def test_density_descent_on_a_smooth_scene(cuda):
     moved_out = (x.detach().norm(dim=-1) > x0.norm(dim=-1)).float().mean()
     print(f"density descent: cost {first:.3e} -> {last:.3e}, {float(moved_out) * 100:.0f} % of the points moved outwards")
     assert last < 0.7 * first and float(moved_out) > 0.95
+
+
+def test_hessian_call_of_the_estimator(cuda):
+    """nav/estimator_helpers.py:297 takes torch.autograd.functional.hessian of measurement_fn.  Upstream the render's backward kernels
+    return plain tensors (their @once_differentiable is commented out), so the second differentiation sees the photometric term's
+    gradient as a constant and the Hessian is that of the torch-side process term alone; the same call must run here, with the same
+    outcome."""
+    from nerfsafetyvalidation_b200.nerf.utils import get_rays
+    model = syn.build_model(blob_scene_weights(), None, None, device=cuda)
+    torch.manual_seed(0)
+    model.update_extra_state()
+    H = W = 24
+    intr = (30.0, 30.0, W / 2, H / 2)
+    true_pose = torch.from_numpy(syn.orbit_pose()[None].astype(np.float32)).to(cuda)
+    target = torch.rand(H * W, 3, generator=torch.Generator().manual_seed(1)).to(cuda)
+
+    def measurement(delta):
+        pose = true_pose.clone()
+        pose[:, :3, 3] = true_pose[:, :3, 3] + delta
+        rays = get_rays(pose, intr, H, W)
+        out = model.render(rays["rays_o"], rays["rays_d"], staged=True, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=MAX_STEPS)
+        return torch.nn.functional.mse_loss(out["image"][0], target) + 3.0 * (delta * delta).sum()
+
+    with model.frozen_weights():
+        hess = torch.autograd.functional.hessian(measurement, torch.zeros(3, device=cuda))
+        grad = torch.autograd.functional.jacobian(measurement, torch.zeros(3, device=cuda))
+    assert torch.allclose(hess, 6.0 * torch.eye(3, device=cuda), atol=1e-6), hess
+    assert float(grad.abs().max()) > 0          # the first derivative does see the photometric term

@@ -141,7 +141,7 @@ int ngp_ctx_set_scene(ngp_ctx *ctx, const uint8_t *bitfield, uint32_t cascade, u
 /* Tunables of ngp_render's epoch policy, per context (the library keeps no process-wide state and reads no environment
  * variables; no upstream counterpart).  name: "rows_per_ray" (sample-buffer rows per ray, default 64), "max_epoch" (cap on the
  * reference iterations per epoch, 0 = none; 1 = one barrier pair per reference iteration), "kshift" (log2 samples per ray per
- * pass, >= 4 = automatic), "t_div", "t_cap", "e0_cap", "rate0_div", "early_cap", "early_steps", "horizon_div" (epoch-length policy),
+ * pass, >= 4 = automatic), "tile_balance" (automatic tile geometry: warp tiles per pipeline below which tiles get shorter, default 4), "t_div", "t_cap", "e0_cap", "rate0_div", "early_cap", "early_steps", "horizon_div" (epoch-length policy),
  * "no_coarse" (1 = march without the coarse occupancy grid).  No option changes any output.  Unknown names are an error. */
 int ngp_ctx_set_option(ngp_ctx *ctx, const char *name, uint64_t value);
 /* Diagnostics for the persistent renderer (no upstream counterpart): when enabled, every warp of ngp_render accumulates

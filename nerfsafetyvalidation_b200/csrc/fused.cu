@@ -498,6 +498,7 @@ struct RenderOptions {
     uint32_t rows_per_ray = 64;   // sample-buffer rows per ray (one epoch's samples of every live ray must fit); 8 B each
     uint32_t max_epoch = 0;       // cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t kshift = 4;          // >= 4: automatic; else log2 of the samples per ray per evaluation pass
+    uint32_t tile_balance = 4;    // automatic K: the smallest K in {2, 4, 8} that still leaves tile_balance warp tiles per pipeline (0 = always 2)
     uint32_t t_div = 2;           // once rays die by transmittance: E = margin / (t_div * rate)
     uint32_t t_cap = 16;          // samples per epoch while transmittance deaths can still move n_step (0 = no cap)
     uint32_t e0_cap = 4;          // cap on E of the first epoch (0 = none)
@@ -532,6 +533,7 @@ struct RenderArgs {
     uint32_t cap_rows;
     uint32_t max_epoch;   // optional cap on E (0 = none); 1 reproduces one barrier pair per reference iteration
     uint32_t force_kshift;   // >= 4: automatic; else log2 of the samples per ray per evaluation pass (profiling A/B)
+    uint32_t tile_balance;   // see RenderOptions
     uint32_t t_div;          // once rays die by transmittance: E = margin / (t_div * rate)
     // iterations-per-epoch caps per n_step (index s - 1), host-computed so the device does no division: cap_n = 128 / s bounds the
     // longest tile; cap_t = 16 / s applies once rays die by transmittance while n_step can still change (s < 8) and bounds what a
@@ -1147,7 +1149,17 @@ __global__ void __launch_bounds__(kRenderThreads, 1) k_render(NetConst nc, Rende
         TileGeom tg;
         for (;;) {   // tile geometry; shrink the epoch until its samples fit the buffer (rarely more than one trip)
             ES = E * s;
-            tg.kshift = ra.force_kshift < 4u ? ra.force_kshift : (ES >= 5u ? 3u : (ES >= 3u ? 2u : ES - 1u));   // K = 8, 4, 2, 1
+            // K samples of R = 32 / K rays per evaluation pass.  A tile's fixed cost (ticket, ray state in and out, SH rows) is per RAY
+            // GROUP, so few long tiles (K = 2: 16 rays) beat many short ones (K = 8: 4 rays) for as long as every one of the SM's 16
+            // pipelines still gets several tiles; near the end of a frame K grows again to keep them evenly loaded.  K <= ES.
+            uint32_t ks = ES >= 5u ? 3u : (ES >= 3u ? 2u : ES - 1u);
+            if (ks > 1u) {
+                const uint32_t want_tiles = ra.tile_balance * gridDim.x * (uint32_t)kGatherWarps;
+                uint32_t k = 1u;
+                while (k < ks && (n_alive >> (5u - k)) < want_tiles) k++;
+                ks = k;
+            }
+            tg.kshift = ra.force_kshift < 4u ? ra.force_kshift : ks;
             tg.ESp = (ES + (1u << tg.kshift) - 1u) & ~((1u << tg.kshift) - 1u);
             const uint32_t R = 32u >> tg.kshift;
             unsigned long long rows = (unsigned long long)((n_alive + R - 1) / R) * R * tg.ESp;
@@ -1744,6 +1756,7 @@ static int render_core(ngp_ctx *c, const float *rays_o, const float *rays_d, uin
     const RenderOptions &op = c->opt;
     ra.max_epoch = op.max_epoch;
     ra.force_kshift = op.kshift;
+    ra.tile_balance = op.tile_balance;
     ra.t_div = op.t_div < 1u ? 1u : op.t_div;
     for (uint32_t k = 1; k <= (uint32_t)kMaxStep; k++) {
         const uint32_t n = (uint32_t)kMaxSamplesPerEpoch / k, t = (op.t_cap ? op.t_cap : (uint32_t)kMaxSamplesPerEpoch) / k;
@@ -1862,7 +1875,7 @@ int ngp_render_poses_host(ngp_ctx *c, const float *poses_host, uint32_t F, uint3
 int ngp_ctx_set_option(ngp_ctx *c, const char *name, uint64_t value) {
     NGP_REQUIRE(c != nullptr && name != nullptr, "ctx_set_option: null argument");
     const struct { const char *name; uint32_t RenderOptions::*field; } table[] = {
-        {"rows_per_ray", &RenderOptions::rows_per_ray}, {"max_epoch", &RenderOptions::max_epoch}, {"kshift", &RenderOptions::kshift},
+        {"rows_per_ray", &RenderOptions::rows_per_ray}, {"max_epoch", &RenderOptions::max_epoch}, {"kshift", &RenderOptions::kshift}, {"tile_balance", &RenderOptions::tile_balance},
         {"t_div", &RenderOptions::t_div}, {"t_cap", &RenderOptions::t_cap}, {"e0_cap", &RenderOptions::e0_cap},
         {"rate0_div", &RenderOptions::rate0_div}, {"no_coarse", &RenderOptions::no_coarse}, {"early_cap", &RenderOptions::early_cap},
         {"early_steps", &RenderOptions::early_steps}, {"horizon_div", &RenderOptions::horizon_div},
@@ -1873,7 +1886,7 @@ int ngp_ctx_set_option(ngp_ctx *c, const char *name, uint64_t value) {
             c->opt.*(t.field) = (uint32_t)value;
             return 0;
         }
-    NGP_REQUIRE(false, "ctx_set_option: unknown option '%s' (rows_per_ray, max_epoch, kshift, t_div, t_cap, e0_cap, rate0_div, no_coarse, early_cap, early_steps, horizon_div)", name);
+    NGP_REQUIRE(false, "ctx_set_option: unknown option '%s' (rows_per_ray, max_epoch, kshift, tile_balance, t_div, t_cap, e0_cap, rate0_div, no_coarse, early_cap, early_steps, horizon_div)", name);
     return 1;
 }
 

@@ -50,7 +50,7 @@ WORKLOADS = {
 
 # The build the committed ncu metrics (profiles/r02_ncu_metrics.json, made by tools/ncu_metrics_json.py from `ncu --set full` captures of
 # k_render on this workload) belong to.  Bump it together with the file; a mismatch reports `traffic: null` instead of a stale number.
-PROFILE_BUILD = "r02h"
+PROFILE_BUILD = "r02j"
 
 
 def ncu_metrics(workload):

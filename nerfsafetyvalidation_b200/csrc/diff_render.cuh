@@ -6,7 +6,8 @@
 //    false for every NGP table, which keeps those paths out of the instruction stream)
 //   k_diff_render<false>   forward: one WARP per ray -- march (32 candidate parameters per step, see march_window) -> 32-sample chunks -> hash grid ->
 //                          both MLPs (mma.sync, fp32 accumulate) -> front-to-back compositing with the T < 1e-4 stop.  Same functions
-//                          as the inference renderer, sample for sample.
+//                          as the inference renderer; a ray is marched as ONE chunk (the reference's batch-dependent chunk restarts can
+//                          move one sample of a few rays in 10^5, see include/ngp_b200.h).
 //   k_diff_render<true>    backward: re-runs the forward of every chunk (nothing but 16 B per ray is kept between the passes) and
 //                          pushes d loss / d image through the compositor (raymarching.cu:606-699), the colour and density MLPs
 //                          (input gradients only: ffmlp.cu's backward with calc_grad_inputs), the SH Jacobian (shencoder.cu:126-355)
